@@ -1,0 +1,216 @@
+#!/usr/bin/env python
+"""Headline benchmark (BASELINE.json): fp64 inverse GFLOP/s + seconds at n=32768, m=128 on N B200s.
+
+One "step" = one complete inversion of the n x n generator matrix |i-j| (reference default,
+main.cpp:52): generator fill + ||A||inf + all Nr elimination steps + singular verdict.  GFLOP/s uses
+the canonical 2 n^3 count (which is also what the engine executes; the reference executes 3 n^3).
+
+    python bench.py --gpus N --steps K --warmup W            # own engine
+    python bench.py --impl reference --gpus N ...            # unmodified reference (CPU, MPI shim)
+    python bench.py --impl baseline --gpus N ...             # in-tree NCCL + cuBLAS baseline
+
+For N > 1 launch with torchrun (one rank per GPU); RANK/LOCAL_RANK/WORLD_SIZE/MASTER_* are read
+from the environment.  Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "fp64_inverse_gflops"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference", "baseline"])
+    ap.add_argument("--n", type=int, default=int(os.environ.get("JB_BENCH_N", "32768")))
+    ap.add_argument("--m", type=int, default=int(os.environ.get("JB_BENCH_M", "128")))
+    ap.add_argument("--formula", type=int, default=1)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--residual", action="store_true", help="also compute ||AX-I|| after the timed region")
+    return ap.parse_args()
+
+
+def flops(n: int) -> float:
+    return 2.0 * float(n) ** 3
+
+
+def run_own(args) -> dict:
+    import torch
+
+    from mpi_jordan_crazy_acceleration_b200.models.eager import formula_rows
+    from mpi_jordan_crazy_acceleration_b200.models.jordan import JordanSolver
+    from mpi_jordan_crazy_acceleration_b200.parallel.comm import Comm
+    from mpi_jordan_crazy_acceleration_b200.utils.timing import ClockSampler
+
+    comm = Comm.init_from_env()
+    if comm.world != args.gpus:
+        if comm.world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torchrun --nproc-per-node N")
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    n, m, W, K = args.n, args.m, max(args.warmup, 0), args.steps
+    s = JordanSolver(n, m, comm=comm, device=local_rank)
+    lay = s.layout
+
+    def one_step():
+        s.fill_formula(args.formula)
+        s.invert_async()
+        s.status()
+
+    for _ in range(W):
+        one_step()
+    # ---------------------------------------------------------------- device-timed region
+    sampler = ClockSampler(local_rank).start() if comm.rank == 0 else None
+    l0 = s.launch_count
+    torch.cuda.synchronize()
+    comm.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.perf_counter()
+    e0.record()
+    for _ in range(K):
+        one_step()
+    e1.record()
+    torch.cuda.synchronize()
+    comm.barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop() if sampler else None
+    ms = comm.allreduce_max(e0.elapsed_time(e1)) / max(K, 1)
+    launches = (s.launch_count - l0)
+    value = flops(n) / (ms * 1e-3) / 1e9
+
+    residual = None
+    if args.residual:
+        residual = s.residual()
+
+    # ---------------------------------------------------------------- end-to-end through the public API
+    e2e = None
+    if not args.no_e2e:
+        rows = torch.tensor(lay.global_rows(), dtype=torch.int64)
+        host = torch.empty(lay.rows_real, n, dtype=torch.float64).pin_memory()
+        chunk = max(1, (1 << 27) // max(n, 1))
+        for a in range(0, lay.rows_real, chunk):  # synthetic |i-j| rows, generated on the host
+            host[a:a + chunk] = formula_rows(args.formula, n, rows[a:a + chunk])
+        corner_bytes = 0
+
+        def e2e_step():
+            nonlocal corner_bytes
+            s.upload_local_rows(host)       # H2D from pinned memory (+ identity padding, norm)
+            s.invert_async()
+            s.status()                      # D2H: singular verdict
+            c = s.corner("X")               # D2H: the reported 10x10 corner of the inverse
+            if c is not None:
+                corner_bytes = c.numel() * 8
+            return c
+
+        e2e_step()
+        torch.cuda.synchronize()
+        comm.barrier()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            e2e_step()
+        torch.cuda.synchronize()
+        comm.barrier()
+        sec = comm.allreduce_max((time.perf_counter() - t0) / max(K, 1))
+        h2d = comm.allreduce_sum_int(lay.rows_real * n * 8)
+        e2e = {"value": flops(n) / sec / 1e9, "unit": "GFLOP/s", "seconds_per_step": sec,
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": corner_bytes + 32 * comm.world,
+               "note": "per step: pinned-host slab -> device, ||A||inf, inversion, verdict + 10x10 corner read back"}
+
+    out = {
+        "metric": METRIC, "value": value, "unit": "GFLOP/s", "n_gpus": comm.world, "steps": K,
+        "warmup": W, "ms_per_step": ms, "seconds_per_inversion": ms * 1e-3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "fp64", "data": "synthetic",
+        "impl": "own",
+        "config": {"model": "block Gauss-Jordan inverse, generator |i-j|", "n": n, "m": m,
+                   "global_batch": 1, "seq_len": n, "parallelism": f"block-cyclic rows x{comm.world}",
+                   "flop_convention": "2n^3 (executed)", "symm": s.symm_mode,
+                   "l2": "inputs (n^2*8 B per inversion) larger than L2; matrix regenerated every step"},
+        "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": t_wall / max(K, 1) * 1e3,
+        "e2e": e2e,
+    }
+    if residual is not None:
+        out["residual"] = residual
+    s.close()
+    return out if comm.rank == 0 else {}
+
+
+def run_baseline(args) -> dict:
+    import torch
+
+    from mpi_jordan_crazy_acceleration_b200.models.eager import EagerJordan
+    from mpi_jordan_crazy_acceleration_b200.parallel.comm import Comm
+
+    comm = Comm.init_from_env()
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    n, m, W, K = args.n, args.m, args.warmup, args.steps
+    e = EagerJordan(n, m, comm=comm, device=f"cuda:{local_rank}")
+
+    def one_step():
+        e.fill_formula(args.formula)
+        e.invert()
+
+    for _ in range(W):
+        one_step()
+    torch.cuda.synchronize()
+    comm.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        one_step()
+    e1.record()
+    torch.cuda.synchronize()
+    comm.barrier()
+    ms = comm.allreduce_max(e0.elapsed_time(e1)) / max(K, 1)
+    out = {"metric": METRIC, "value": flops(n) / (ms * 1e-3) / 1e9, "unit": "GFLOP/s",
+           "n_gpus": comm.world, "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "fp64", "data": "synthetic",
+           "impl": "baseline-nccl-cublas", "config": {"n": n, "m": m}}
+    return out if comm.rank == 0 else {}
+
+
+def run_reference(args) -> dict:
+    sys.path.insert(0, os.path.join(ROOT, "baseline", "ref_cpu"))
+    try:
+        import run_reference as rr
+    except Exception as exc:  # noqa: BLE001
+        return {"impl": "reference", "unavailable": f"reference harness missing: {exc!r}"}
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return {}
+    return rr.bench_line(args.n, args.m, args.gpus, args.steps, args.warmup, METRIC)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        out = run_reference(args)
+    elif args.impl == "baseline":
+        out = run_baseline(args)
+    else:
+        out = run_own(args)
+    if out:
+        print(json.dumps(out), flush=True)
+    try:
+        import torch.distributed as dist
+
+        if dist.is_initialized():
+            dist.barrier()
+            dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        pass
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,600 @@
+// Host-side engine: owns the per-rank buffers, builds the TMA descriptors once, and enqueues the
+// whole elimination (Nr steps x {K1 pivot search + min-loc, fused scale/broadcast/update}) on one
+// stream with no host synchronisation: the pivot choice of every step stays in device memory.
+// This is the B200 replacement of solve()/Jordan() (main.cpp:343-519, 953-1204).
+#include <stdarg.h>
+#include <string.h>
+#include <algorithm>
+#include <vector>
+#include "common.cuh"
+#include "engine_types.h"
+#include "kernels.h"
+#include "../include/jordan_b200.h"
+
+static thread_local char g_err[512] = "";
+void jb_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* jb_last_error(void) { return g_err; }
+
+namespace {
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 2-D fp64 tensor map: inner dimension `cols` (contiguous), `rows` rows of pitch ld doubles.
+int make_map(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t ld,
+             uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    jb_set_error("cuTensorMapEncodeTiled entry point not available");
+    return JB_ERR_CUDA;
+  }
+  cuuint64_t gdim[2] = {cols ? cols : 1, rows ? rows : 1};
+  cuuint64_t gstr[1] = {ld * sizeof(double)};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<void*>(base), gdim, gstr, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    jb_set_error("cuTensorMapEncodeTiled failed: %d (cols=%llu rows=%llu ld=%llu box=%ux%u)", (int)r,
+                 (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)ld, box_cols,
+                 box_rows);
+    return JB_ERR_CUDA;
+  }
+  return JB_OK;
+}
+
+}  // namespace
+
+struct JbEngine {
+  JbConfig cfg;
+  int64_t n, Nr, ldw, rows_loc;
+  int m, p, rank, Kp, rloc, nsub, CT, sm_count;
+  // local buffers
+  double *W = nullptr, *Lbuf = nullptr, *invbuf = nullptr, *normbuf = nullptr, *Acopy = nullptr;
+  int* okbuf = nullptr;
+  JbCtl* ctl = nullptr;
+  JbStepInfo* stepinfo = nullptr;
+  double *Xp = nullptr, *rowsum = nullptr, *scratch_max = nullptr, *Rslab = nullptr;
+  // symmetric region
+  size_t off_rowbuf[2], off_swapbuf, off_rowflag[2], off_swapflag, off_mail, symm_bytes;
+  unsigned char* symm_peers[JB_MAX_RANKS] = {nullptr};
+  unsigned char* symm_mc = nullptr;
+  bool own_symm = false, symm_ready = false;
+  bool peers_opened[2] = {false, false};
+  const double* W_peers[JB_MAX_RANKS] = {nullptr};
+  StepMaps maps[2];
+  bool maps_ready = false;
+  uint32_t gstep = 0;  // global step counter (same on every rank)
+  int64_t launches = 0;
+  bool norm_set = false;
+};
+
+namespace {
+
+int build_maps(JbEngine* e) {
+  unsigned char* loc = e->symm_peers[e->rank];
+  for (int par = 0; par < 2; ++par) {
+    StepMaps& M = e->maps[par];
+    int rc;
+    if ((rc = make_map(&M.tmW, e->W, e->ldw, e->rows_loc, e->ldw, JB_RS, JB_BK))) return rc;
+    if ((rc = make_map(&M.tmRow, loc + e->off_rowbuf[par], e->ldw, e->Kp, e->ldw, JB_RS, JB_BK)))
+      return rc;
+    if ((rc = make_map(&M.tmL, e->Lbuf, e->Kp, e->rows_loc, e->Kp, JB_LS, JB_BM))) return rc;
+    if ((rc = make_map(&M.tmInv, e->invbuf, e->Kp, (uint64_t)e->rloc * e->Kp, e->Kp, JB_LS, JB_BM)))
+      return rc;
+    if ((rc = make_map(&M.tmSwap, loc + e->off_swapbuf, e->ldw, e->Kp, e->ldw, JB_LS, JB_BM)))
+      return rc;
+  }
+  e->maps_ready = true;
+  return JB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
+  if (!cfg || !out || cfg->n <= 0 || cfg->m <= 0 || cfg->p <= 0 || cfg->p > JB_MAX_RANKS ||
+      cfg->rank < 0 || cfg->rank >= cfg->p) {
+    jb_set_error("jb_engine_create: bad configuration");
+    return JB_ERR_ARG;
+  }
+  if (jb_k1_cluster_size(cfg->m) == 0) {
+    jb_set_error("block size m=%d does not fit distributed shared memory (max ~440)", cfg->m);
+    return JB_ERR_ARG;
+  }
+  JB_CHECK(cudaSetDevice(cfg->device));
+  JbEngine* e = new JbEngine();
+  e->cfg = *cfg;
+  e->n = cfg->n;
+  e->m = cfg->m;
+  e->p = cfg->p;
+  e->rank = cfg->rank;
+  e->Nr = jb_num_block_rows(e->n, e->m);
+  e->rloc = (int)jb_rows_per_process(e->Nr, e->p, e->rank);
+  e->rows_loc = (int64_t)e->rloc * e->m;
+  e->ldw = jb_padded_ld(e->n, e->m);
+  e->Kp = (int)align_up((size_t)e->m, JB_BK);
+  e->nsub = (e->m + JB_BM - 1) / JB_BM;
+  e->CT = (int)((e->ldw + JB_BN - 1) / JB_BN);
+  cudaDeviceProp prop;
+  JB_CHECK(cudaGetDeviceProperties(&prop, cfg->device));
+  e->sm_count = prop.multiProcessorCount;
+
+  auto dmalloc = [&](void** ptr, size_t bytes) -> cudaError_t {
+    cudaError_t r = cudaMalloc(ptr, bytes ? bytes : 256);
+    if (r == cudaSuccess) r = cudaMemset(*ptr, 0, bytes ? bytes : 256);
+    return r;
+  };
+  const size_t rl = (size_t)std::max<int64_t>(e->rows_loc, 1);
+  cudaError_t r = cudaSuccess;
+  if (r == cudaSuccess) r = dmalloc((void**)&e->W, rl * e->ldw * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf, (rl + JB_BM) * e->Kp * 8);
+  if (r == cudaSuccess)
+    r = dmalloc((void**)&e->invbuf, ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->normbuf, (size_t)std::max(e->rloc, 1) * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->okbuf, (size_t)std::max(e->rloc, 1) * 4);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->ctl, sizeof(JbCtl));
+  if (r == cudaSuccess) r = dmalloc((void**)&e->stepinfo, (size_t)e->Nr * sizeof(JbStepInfo));
+  if (r == cudaSuccess) r = dmalloc((void**)&e->rowsum, rl * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->scratch_max, 64);
+  if (r == cudaSuccess && cfg->keep_copy) r = dmalloc((void**)&e->Acopy, rl * e->ldw * 8);
+  if (r != cudaSuccess) {
+    jb_set_error("Not enough memory! (%s)", cudaGetErrorString(r));  // main.cpp:375
+    jb_engine_destroy(e);
+    return JB_ERR_NOMEM;
+  }
+  // symmetric region layout
+  size_t off = 0;
+  const size_t rb = align_up((size_t)e->Kp * e->ldw * 8, 256);
+  e->off_rowbuf[0] = off; off += rb;
+  e->off_rowbuf[1] = off; off += rb;
+  e->off_swapbuf = off; off += rb;
+  const size_t fb = align_up((size_t)e->CT * 4, 256);
+  e->off_rowflag[0] = off; off += fb;
+  e->off_rowflag[1] = off; off += fb;
+  e->off_swapflag = off; off += fb;
+  e->off_mail = off; off += align_up(2 * JB_MAX_RANKS * sizeof(JbMail), 256);
+  e->symm_bytes = align_up(off, 4096);
+  e->W_peers[e->rank] = e->W;
+  *out = e;
+  return JB_OK;
+}
+
+void jb_engine_destroy(JbEngine* e) {
+  if (!e) return;
+  cudaSetDevice(e->cfg.device);
+  cudaDeviceSynchronize();
+  for (int which = 0; which < 2; ++which)
+    if (e->peers_opened[which])
+      for (int r = 0; r < e->p; ++r)
+        if (r != e->rank) {
+          void* ptr = which == 0 ? (void*)e->symm_peers[r] : (void*)e->W_peers[r];
+          if (ptr) cudaIpcCloseMemHandle(ptr);
+        }
+  if (e->own_symm && e->symm_peers[e->rank]) cudaFree(e->symm_peers[e->rank]);
+  cudaFree(e->W); cudaFree(e->Lbuf); cudaFree(e->invbuf); cudaFree(e->normbuf); cudaFree(e->okbuf);
+  cudaFree(e->ctl); cudaFree(e->stepinfo); cudaFree(e->rowsum); cudaFree(e->scratch_max);
+  cudaFree(e->Acopy); cudaFree(e->Xp); cudaFree(e->Rslab);
+  delete e;
+}
+
+size_t jb_engine_symm_bytes(const JbEngine* e) { return e->symm_bytes; }
+
+int jb_engine_alloc_symm(JbEngine* e) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  void* ptr = nullptr;
+  if (cudaMalloc(&ptr, e->symm_bytes) != cudaSuccess) {
+    jb_set_error("Not enough memory! (symmetric region, %zu bytes)", e->symm_bytes);
+    return JB_ERR_NOMEM;
+  }
+  JB_CHECK(cudaMemset(ptr, 0, e->symm_bytes));
+  e->symm_peers[e->rank] = (unsigned char*)ptr;
+  e->own_symm = true;
+  if (e->p == 1) {
+    e->symm_ready = true;
+    return build_maps(e);
+  }
+  return JB_OK;
+}
+
+int jb_engine_bind_symm(JbEngine* e, void* const* peer_ptrs, void* multicast_ptr) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  for (int r = 0; r < e->p; ++r) {
+    if (!peer_ptrs[r]) {
+      jb_set_error("jb_engine_bind_symm: null peer pointer for rank %d", r);
+      return JB_ERR_ARG;
+    }
+    e->symm_peers[r] = (unsigned char*)peer_ptrs[r];
+  }
+  e->symm_mc = (unsigned char*)multicast_ptr;
+  e->symm_ready = true;
+  return build_maps(e);
+}
+
+int jb_engine_ipc_handle(JbEngine* e, int which, void* handle64) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  cudaIpcMemHandle_t h;
+  void* ptr = which == 0 ? (void*)e->symm_peers[e->rank] : (void*)e->W;
+  if (!ptr) {
+    jb_set_error("jb_engine_ipc_handle: region %d not allocated", which);
+    return JB_ERR_ARG;
+  }
+  JB_CHECK(cudaIpcGetMemHandle(&h, ptr));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return JB_OK;
+}
+
+int jb_engine_open_peers(JbEngine* e, int which, const void* handles) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  for (int r = 0; r < e->p; ++r) {
+    if (r == e->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + 64 * r, 64);
+    void* ptr = nullptr;
+    JB_CHECK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    if (which == 0) e->symm_peers[r] = (unsigned char*)ptr;
+    else e->W_peers[r] = (const double*)ptr;
+  }
+  e->peers_opened[which] = true;
+  if (which == 0) {
+    e->symm_ready = true;
+    return build_maps(e);
+  }
+  return JB_OK;
+}
+
+int jb_engine_reset_sync(JbEngine* e) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  JB_CHECK(cudaDeviceSynchronize());
+  unsigned char* loc = e->symm_peers[e->rank];
+  if (loc) JB_CHECK(cudaMemset(loc + e->off_rowflag[0], 0, e->symm_bytes - e->off_rowflag[0]));
+  JB_CHECK(cudaMemset(e->ctl, 0, offsetof(JbCtl, norm_a)));
+  JB_CHECK(cudaDeviceSynchronize());
+  e->gstep = 0;
+  return JB_OK;
+}
+
+int jb_engine_fill_formula(JbEngine* e, int formula, void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  JB_CHECK(cudaMemsetAsync(e->scratch_max, 0, 8, st));
+  FillParams P;
+  P.W = e->W; P.ldw = e->ldw; P.n = e->n; P.m = e->m; P.p = e->p; P.rank = e->rank;
+  P.rloc = e->rloc; P.formula = formula; P.rowsum_max = e->scratch_max;
+  JB_CHECK(jb_launch_fill(P, st));
+  e->launches += (e->rows_loc > 0);
+  if (e->Acopy)
+    JB_CHECK(cudaMemcpyAsync(e->Acopy, e->W, (size_t)e->rows_loc * e->ldw * 8,
+                             cudaMemcpyDeviceToDevice, st));
+  return JB_OK;
+}
+
+int jb_engine_upload_rows(JbEngine* e, const double* host_rows, int64_t local_row0, int64_t nrows,
+                          void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  if (local_row0 < 0 || local_row0 + nrows > e->rows_loc) {
+    jb_set_error("jb_engine_upload_rows: rows out of range");
+    return JB_ERR_ARG;
+  }
+  JB_CHECK(cudaMemcpy2DAsync(e->W + local_row0 * e->ldw, (size_t)e->ldw * 8, host_rows,
+                             (size_t)e->n * 8, (size_t)e->n * 8, (size_t)nrows,
+                             cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return JB_OK;
+}
+
+// identity padding of rows / columns >= n (formula 0 = keep what was uploaded)
+__global__ void k_pad_identity(double* W, int64_t ldw, int64_t n, int m, int p, int rank,
+                               int64_t rows) {
+  for (int64_t lr = blockIdx.x; lr < rows; lr += gridDim.x) {
+    const int64_t gi = ((lr / m) * p + rank) * m + lr % m;
+    const int64_t j0 = (gi >= n) ? 0 : n;
+    for (int64_t j = j0 + threadIdx.x; j < ldw; j += blockDim.x)
+      W[lr * ldw + j] = (gi == j) ? 1.0 : 0.0;
+  }
+}
+
+int jb_engine_finish_upload(JbEngine* e, void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (e->rows_loc > 0) {
+    int grid = (int)std::min<int64_t>(e->rows_loc, 148 * 16);
+    k_pad_identity<<<grid, 256, 0, st>>>(e->W, e->ldw, e->n, e->m, e->p, e->rank, e->rows_loc);
+    JB_CHECK(cudaGetLastError());
+    e->launches++;
+  }
+  JB_CHECK(cudaMemsetAsync(e->scratch_max, 0, 8, st));
+  // ||A||inf over the real rows only: padded rows have row sum 1 and are excluded by n-wide sums
+  // of rows gi < n; rows gi >= n contribute |1| which is harmless only if ||A|| >= 1, so mask them.
+  int64_t real_rows = 0;
+  for (int64_t lr = 0; lr < e->rows_loc; ++lr)
+    if (jb_local_to_global_row(lr, e->m, e->p, e->rank) < e->n) real_rows = lr + 1;
+  JB_CHECK(jb_launch_rowsum_max(e->W, real_rows, e->n, e->ldw, e->scratch_max, st));
+  e->launches += (real_rows > 0);
+  if (e->Acopy)
+    JB_CHECK(cudaMemcpyAsync(e->Acopy, e->W, (size_t)e->rows_loc * e->ldw * 8,
+                             cudaMemcpyDeviceToDevice, st));
+  return JB_OK;
+}
+
+int jb_engine_local_norm(JbEngine* e, double* out) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  JB_CHECK(cudaDeviceSynchronize());
+  JB_CHECK(cudaMemcpy(out, e->scratch_max, 8, cudaMemcpyDeviceToHost));
+  return JB_OK;
+}
+
+int jb_engine_set_norm(JbEngine* e, double global_norm) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  JB_CHECK(cudaMemcpy(&e->ctl->norm_a, &global_norm, 8, cudaMemcpyHostToDevice));
+  e->norm_set = true;
+  return JB_OK;
+}
+
+int jb_engine_invert(JbEngine* e, void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  if (!e->symm_ready || !e->maps_ready) {
+    jb_set_error("jb_engine_invert: symmetric region not bound (alloc_symm/bind_symm/open_peers)");
+    return JB_ERR_ARG;
+  }
+  if (!e->norm_set) {
+    jb_set_error("jb_engine_invert: jb_engine_set_norm was not called");
+    return JB_ERR_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  JB_CHECK(cudaMemsetAsync(e->ctl, 0, offsetof(JbCtl, norm_a), st));
+
+  K1Params K;
+  K.W = e->W; K.Lbuf = e->Lbuf; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
+  K.ctl = e->ctl; K.stepinfo = e->stepinfo;
+  for (int r = 0; r < JB_MAX_RANKS; ++r)
+    K.mail_peers[r] = r < e->p ? (JbMail*)(e->symm_peers[r] + e->off_mail) : nullptr;
+  K.ldw = e->ldw; K.m = e->m; K.Kp = e->Kp; K.p = e->p; K.rank = e->rank; K.rloc = e->rloc;
+
+  StepParams S;
+  S.W = e->W; S.invbuf = e->invbuf; S.stepinfo = e->stepinfo; S.ctl = e->ctl;
+  S.ldw = e->ldw; S.m = e->m; S.Kp = e->Kp; S.p = e->p; S.rank = e->rank;
+  S.rloc = e->rloc; S.nsub = e->nsub; S.CT = e->CT;
+  for (int r = 0; r < JB_MAX_RANKS; ++r) {
+    S.swapbuf_peers[r] = r < e->p ? (double*)(e->symm_peers[r] + e->off_swapbuf) : nullptr;
+    S.swapflag_peers[r] = r < e->p ? (uint32_t*)(e->symm_peers[r] + e->off_swapflag) : nullptr;
+  }
+  const int grid = 2 * e->sm_count;
+  const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
+
+  for (int64_t t = 0; t < e->Nr; ++t) {
+    const uint32_t g = e->gstep++;
+    const int par = g & 1;
+    // ---- K1: candidates are local block rows with global index >= t (main.cpp:1028)
+    int64_t s0 = t > e->rank ? (t - e->rank + e->p - 1) / e->p : 0;
+    K.t = (int)t;
+    K.s0 = (int)s0;
+    K.ncand = (int)std::max<int64_t>(0, e->rloc - s0);
+    K.ngroups = std::max(K.ncand, 1);
+    K.tag = g + 1;
+    JB_CHECK(jb_launch_k1(K, panel_ctas, st));
+    // ---- fused scale + broadcast + swap + trailing update
+    S.t = (int)t;
+    S.t_slot = (t % e->p == e->rank) ? (int)(t / e->p) : -1;
+    S.row_expect = ((g >> 1) + 1) * (uint32_t)e->nsub;
+    S.tag = g + 1;
+    for (int r = 0; r < JB_MAX_RANKS; ++r) {
+      S.rowbuf_peers[r] = r < e->p ? (double*)(e->symm_peers[r] + e->off_rowbuf[par]) : nullptr;
+      S.rowflag_peers[r] = r < e->p ? (uint32_t*)(e->symm_peers[r] + e->off_rowflag[par]) : nullptr;
+    }
+    S.rowbuf_mc = e->symm_mc ? (double*)(e->symm_mc + e->off_rowbuf[par]) : nullptr;
+    S.rowflag_mc = e->symm_mc ? (uint32_t*)(e->symm_mc + e->off_rowflag[par]) : nullptr;
+    JB_CHECK(jb_launch_step(S, e->maps[par], grid, st));
+    e->launches += 2;
+  }
+  JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
+  e->launches += (e->rows_loc > 0);
+  return JB_OK;
+}
+
+int jb_engine_status(JbEngine* e, void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  JB_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+  JbCtl c;
+  JB_CHECK(cudaMemcpy(&c, e->ctl, sizeof(c), cudaMemcpyDeviceToHost));
+  if (c.singular) {
+    jb_set_error("singular matrix");  // main.cpp:438
+    return JB_ERR_SINGULAR;
+  }
+  return JB_OK;
+}
+
+int jb_engine_pivots(JbEngine* e, int32_t* piv_out) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  std::vector<JbStepInfo> si((size_t)e->Nr);
+  JB_CHECK(cudaMemcpy(si.data(), e->stepinfo, si.size() * sizeof(JbStepInfo), cudaMemcpyDeviceToHost));
+  for (int64_t t = 0; t < e->Nr; ++t) piv_out[t] = si[t].piv_g;
+  return JB_OK;
+}
+
+int64_t jb_engine_launch_count(const JbEngine* e) { return e->launches; }
+void* jb_engine_w_ptr(JbEngine* e) { return e->W; }
+int64_t jb_engine_ldw(const JbEngine* e) { return e->ldw; }
+int64_t jb_engine_local_rows(const JbEngine* e) { return e->rows_loc; }
+
+int jb_engine_download(JbEngine* e, int which, int64_t local_row0, int64_t nrows, int64_t col0,
+                       int64_t ncols, double* host, int64_t ldh) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  const double* src = which == 0 ? e->W : e->Acopy;
+  if (!src || local_row0 < 0 || local_row0 + nrows > e->rows_loc || col0 + ncols > e->ldw) {
+    jb_set_error("jb_engine_download: bad region");
+    return JB_ERR_ARG;
+  }
+  if (nrows == 0 || ncols == 0) return JB_OK;
+  JB_CHECK(cudaMemcpy2D(host, (size_t)ldh * 8, src + local_row0 * e->ldw + col0, (size_t)e->ldw * 8,
+                        (size_t)ncols * 8, (size_t)nrows, cudaMemcpyDeviceToHost));
+  return JB_OK;
+}
+
+static int ensure_panel(JbEngine* e) {
+  if (!e->Xp) {
+    if (cudaMalloc((void**)&e->Xp, (size_t)e->n * 1024 * 8) != cudaSuccess) {
+      jb_set_error("Not enough memory! (X panel)");
+      return JB_ERR_NOMEM;
+    }
+  }
+  return JB_OK;
+}
+
+// generic panel loop: for each 1024-wide column panel gather the right operand from the peers'
+// slabs `right_peers` and multiply with the left operand.
+static int panel_gemm(JbEngine* e, const double* const* right_peers, const double* left,
+                      int formula, int mode, double* C, const double* Cin, cudaStream_t st) {
+  int rc = ensure_panel(e);
+  if (rc) return rc;
+  const int PW = 1024;
+  for (int64_t col0 = 0; col0 < e->n; col0 += PW) {
+    const int pw = (int)std::min<int64_t>(PW, e->ldw - col0);
+    GatherParams G;
+    for (int r = 0; r < JB_MAX_RANKS; ++r) G.X_peers[r] = r < e->p ? right_peers[r] : nullptr;
+    G.ldx = e->ldw; G.Xp = e->Xp; G.ldxp = PW; G.n = e->n; G.col0 = col0; G.m = e->m; G.p = e->p;
+    G.pw = pw;
+    JB_CHECK(jb_launch_gather_panel(G, st));
+    DistGemmParams D;
+    D.A = left; D.lda = e->ldw; D.formula = formula; D.Xp = e->Xp; D.ldxp = PW; D.col0 = col0;
+    D.pw = pw; D.C = C; D.ldc = e->ldw; D.Cin = Cin; D.ldcin = e->ldw; D.rowsum = e->rowsum;
+    D.n = e->n; D.m = e->m; D.p = e->p; D.rank = e->rank; D.rloc = e->rloc; D.mode = mode;
+    JB_CHECK(jb_launch_dist_gemm(D, st));
+    e->launches += 1 + (e->rows_loc > 0);
+  }
+  return JB_OK;
+}
+
+int jb_engine_residual(JbEngine* e, int formula, double* out_local, void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int r = 0; r < e->p; ++r)
+    if (!e->W_peers[r]) {
+      jb_set_error("jb_engine_residual: peer slabs not opened (jb_engine_open_peers(which=1))");
+      return JB_ERR_ARG;
+    }
+  const double* left = nullptr;
+  if (formula < 0) {
+    if (!e->Acopy) {
+      jb_set_error("jb_engine_residual: no kept copy of A (keep_copy=0)");
+      return JB_ERR_ARG;
+    }
+    left = e->Acopy;
+  }
+  JB_CHECK(cudaMemsetAsync(e->rowsum, 0, (size_t)std::max<int64_t>(e->rows_loc, 1) * 8, st));
+  JB_CHECK(cudaMemsetAsync(e->scratch_max, 0, 8, st));
+  int rc = panel_gemm(e, e->W_peers, left, formula, JB_GEMM_RESIDUAL, nullptr, nullptr, st);
+  if (rc) return rc;
+  JB_CHECK(jb_launch_max_reduce(e->rowsum, e->rows_loc, e->scratch_max, st));
+  e->launches += (e->rows_loc > 0);
+  JB_CHECK(cudaStreamSynchronize(st));
+  JB_CHECK(cudaMemcpy(out_local, e->scratch_max, 8, cudaMemcpyDeviceToHost));
+  return JB_OK;
+}
+
+// Newton-Schulz refinement X <- X + X (I - A X), split in two collective phases so the caller can
+// place a cross-rank barrier between them:
+//   phase 0: Rslab = I - A X         (right operand X gathered from all ranks)
+//   phase 1: X    = X + X * R        (right operand R gathered from all ranks' Rslab)
+// Peer access to Rslab goes through the same IPC mapping as W: Rslab lives in the second half of
+// nothing shared, so phase 1 is only available for p == 1 unless W_peers-style handles for Rslab
+// were exchanged by the caller (see python parallel/comm.py which does that for p > 1).
+int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream) {
+  JB_CHECK(cudaSetDevice(e->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t slab = (size_t)std::max<int64_t>(e->rows_loc, 1) * e->ldw * 8;
+  if (!e->Rslab) {
+    if (cudaMalloc((void**)&e->Rslab, 2 * slab) != cudaSuccess) {
+      jb_set_error("Not enough memory! (refinement slabs)");
+      return JB_ERR_NOMEM;
+    }
+    JB_CHECK(cudaMemset(e->Rslab, 0, 2 * slab));
+  }
+  double* R = e->Rslab;
+  double* Xnew = e->Rslab + slab / 8;
+  if (e->p != 1) {
+    jb_set_error("jb_engine_refine_phase: multi-rank refinement is driven from the Python layer");
+    return JB_ERR_ARG;
+  }
+  const double* left = formula < 0 ? e->Acopy : nullptr;
+  if (formula < 0 && !left) {
+    jb_set_error("jb_engine_refine_phase: no kept copy of A");
+    return JB_ERR_ARG;
+  }
+  if (phase == 0) {
+    return panel_gemm(e, e->W_peers, left, formula, JB_GEMM_STORE_R, R, nullptr, st);
+  } else {
+    const double* rp[JB_MAX_RANKS] = {nullptr};
+    rp[0] = R;
+    int rc = panel_gemm(e, rp, e->W, 0, JB_GEMM_XPLUS, Xnew, e->W, st);
+    if (rc) return rc;
+    JB_CHECK(cudaMemcpyAsync(e->W, Xnew, slab, cudaMemcpyDeviceToDevice, st));
+    return JB_OK;
+  }
+}
+
+// Stand-alone batched block inversion (tests, tools): blocks stacked vertically, [nblocks*m][m].
+int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
+                     double* d_inv, double* d_norms, int32_t* d_ok, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (jb_k1_cluster_size(m) == 0 || nblocks <= 0) {
+    jb_set_error("jb_block_inverse: unsupported m=%d or nblocks", m);
+    return JB_ERR_ARG;
+  }
+  const int Kp = (int)align_up((size_t)m, JB_BK);
+  unsigned char* scratch = nullptr;
+  const size_t inv_bytes = (size_t)nblocks * Kp * Kp * 8;
+  const size_t lbuf_bytes = (size_t)nblocks * m * Kp * 8;
+  const size_t total = inv_bytes + lbuf_bytes + 4096 + (size_t)sizeof(JbStepInfo) * 2;
+  JB_CHECK(cudaMalloc((void**)&scratch, total));
+  JB_CHECK(cudaMemsetAsync(scratch, 0, total, st));
+  K1Params K;
+  memset(&K, 0, sizeof(K));
+  K.W = d_blocks;
+  K.invbuf = (double*)scratch;
+  K.Lbuf = (double*)(scratch + inv_bytes);
+  unsigned char* tail = scratch + inv_bytes + lbuf_bytes;
+  K.ctl = (JbCtl*)tail;
+  K.mail_peers[0] = (JbMail*)(tail + 256);
+  K.stepinfo = (JbStepInfo*)(tail + 256 + 2 * JB_MAX_RANKS * sizeof(JbMail));
+  K.normbuf = d_norms;
+  K.okbuf = d_ok;
+  K.ldw = m; K.m = m; K.Kp = Kp; K.p = 1; K.rank = 0; K.t = 0; K.rloc = (int)nblocks;
+  K.s0 = 0; K.ncand = (int)nblocks; K.ngroups = (int)nblocks; K.tag = 1;
+  JB_CHECK(cudaMemcpyAsync(&K.ctl->norm_a, &norm_a, 8, cudaMemcpyHostToDevice, st));
+  JB_CHECK(cudaMemsetAsync(d_ok, 0, (size_t)nblocks * 4, st));
+  JB_CHECK(jb_launch_k1(K, 1, st));
+  for (int64_t b = 0; b < nblocks; ++b)
+    JB_CHECK(cudaMemcpy2DAsync(d_inv + b * m * m, (size_t)m * 8, K.invbuf + b * Kp * Kp,
+                               (size_t)Kp * 8, (size_t)m * 8, (size_t)m, cudaMemcpyDeviceToDevice,
+                               st));
+  JB_CHECK(cudaStreamSynchronize(st));
+  JB_CHECK(cudaFree(scratch));
+  return JB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,106 @@
+// Kernel parameter blocks and host-side launchers (internal to libjordan_b200).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "engine_types.h"
+
+// ------------------------------------------------------------------ K1 pivot search + min-loc
+struct K1Params {
+  const double* W;     // local rows, ld = ldw
+  double* Lbuf;        // [rloc*m][Kp] copy of block-column t
+  double* invbuf;      // [rloc][Kp][Kp] inverse of each candidate
+  double* normbuf;     // [rloc]
+  int* okbuf;          // [rloc]
+  JbCtl* ctl;
+  JbStepInfo* stepinfo;
+  JbMail* mail_peers[JB_MAX_RANKS];  // every rank's mailbox ([2][JB_MAX_RANKS]); [rank] is local
+  int64_t ldw;
+  int m, Kp, p, rank, t;
+  int rloc;     // local block rows
+  int s0;       // first candidate slot (global index >= t)
+  int ncand;    // number of candidates on this rank (may be 0)
+  int ngroups;  // max(ncand, 1) CTA groups doing inversion / min-loc
+  uint32_t tag; // global step counter + 1
+};
+int jb_k1_cluster_size(int m);
+cudaError_t jb_launch_k1(const K1Params& P, int panel_ctas, cudaStream_t st);
+
+// ------------------------------------------------------------------ fused step kernel (K2+K3+K4)
+struct StepParams {
+  double* W;
+  const double* invbuf;
+  const JbStepInfo* stepinfo;
+  const JbCtl* ctl;
+  double* rowbuf_peers[JB_MAX_RANKS];     // rowbuf[par] on every rank
+  uint32_t* rowflag_peers[JB_MAX_RANKS];  // rowflag[par] on every rank
+  double* swapbuf_peers[JB_MAX_RANKS];
+  uint32_t* swapflag_peers[JB_MAX_RANKS];
+  double* rowbuf_mc;      // NVLS multicast alias of rowbuf[par] (nullptr -> unicast peer stores)
+  uint32_t* rowflag_mc;   // NVLS multicast alias of rowflag[par]
+  int64_t ldw;
+  int m, Kp, p, rank, t;
+  int rloc, nsub, CT;
+  int t_slot;             // local slot of block row t on its owner, else -1
+  uint32_t row_expect;    // rowflag value meaning "tile landed"
+  uint32_t tag;           // swapflag value for this step
+};
+struct StepMaps {
+  CUtensorMap tmW;     // W              box {JB_RS, JB_BK}
+  CUtensorMap tmRow;   // rowbuf[par]    box {JB_RS, JB_BK}
+  CUtensorMap tmL;     // Lbuf           box {JB_LS, JB_BM}
+  CUtensorMap tmInv;   // invbuf         box {JB_LS, JB_BM}
+  CUtensorMap tmSwap;  // swapbuf        box {JB_LS, JB_BM}
+};
+size_t jb_step_smem_bytes();
+cudaError_t jb_launch_step(const StepParams& P, const StepMaps& M, int grid, cudaStream_t st);
+
+// ------------------------------------------------------------------ K5 generator fill + norm
+struct FillParams {
+  double* W;
+  int64_t ldw, n;
+  int m, p, rank, rloc, formula;
+  double* rowsum_max;  // device double, atomic max of abs row sums (local ||A||inf)
+};
+cudaError_t jb_launch_fill(const FillParams& P, cudaStream_t st);
+cudaError_t jb_launch_rowsum_max(const double* W, int64_t rows, int64_t cols, int64_t ld,
+                                 double* out_max, cudaStream_t st);
+
+// ------------------------------------------------------------------ final column un-permutation
+cudaError_t jb_launch_unpermute(double* W, int64_t rows, int64_t ldw, int m, int Nr,
+                                const JbStepInfo* stepinfo, cudaStream_t st);
+
+// ------------------------------------------------------------------ K6/K7 distributed GEMM
+// C_loc (rows_loc x n) = A_loc (rows_loc x n; formula-generated or stored) * X (n x n, block-cyclic
+// rows spread over the ranks).  A column panel of X is first pulled from the owning peers' HBM
+// into a local staging panel (k_gather_panel), then multiplied on the FP64 tensor cores.
+enum { JB_GEMM_RESIDUAL = 0, JB_GEMM_STORE_R = 1, JB_GEMM_XPLUS = 2 };
+struct GatherParams {
+  const double* X_peers[JB_MAX_RANKS];  // every rank's local slab (block-cyclic rows), ld = ldx
+  int64_t ldx;
+  double* Xp;                           // local panel [n][ldxp], rows in GLOBAL order
+  int64_t ldxp;
+  int64_t n, col0;
+  int m, p, pw;
+};
+struct DistGemmParams {
+  const double* A;      // stored left operand, local rows (nullptr -> generator formula)
+  int64_t lda;
+  int formula;
+  const double* Xp;     // gathered right-operand panel [n][ldxp]
+  int64_t ldxp;
+  int64_t col0;         // first global column covered by the panel
+  int pw;               // panel width
+  double* C;            // output slab (STORE_R / XPLUS)
+  int64_t ldc;
+  const double* Cin;    // XPLUS: C = Cin + A*Xp
+  int64_t ldcin;
+  double* rowsum;       // RESIDUAL: [rows_loc] abs row sums, accumulated with atomics
+  int64_t n;
+  int m, p, rank, rloc, mode;
+};
+cudaError_t jb_launch_gather_panel(const GatherParams& P, cudaStream_t st);
+cudaError_t jb_launch_dist_gemm(const DistGemmParams& P, cudaStream_t st);
+cudaError_t jb_launch_max_reduce(const double* v, int64_t count, double* out, cudaStream_t st);
+
+#include "kernels_formula.h"

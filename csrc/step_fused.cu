@@ -1,0 +1,337 @@
+// Fused elimination-step kernel (K2 `pivot_row_scale_mcast` + K3 `trailing_update_f64` + K4 row swap).
+//
+// One persistent launch per step and rank.  CTAs walk a common work list:
+//   SCALE items (pivot owner only): R_j = P^-1 * W(piv, j) on FP64 tensor cores, result written
+//       straight into EVERY rank's pivot-row buffer (NVLS multimem.st, or unicast peer stores when
+//       no multicast object is bound), then a per-column-tile flag is bumped on every rank.
+//   ROWT items (owner of block row t): push the old row t into the pivot owner's swap buffer over
+//       NVLink (the block-row swap of main.cpp:1100-1131 done with peer stores instead of
+//       MPI_Send/Recv), then replace row t by the scaled pivot row.
+//   UPD  items (every rank): C(i,j) -= A(i,t) * R_j for all local rows, DMMA m8n8k4, operands fed by
+//       TMA (cp.async.bulk.tensor) through a 4-stage mbarrier ring.  A consumer tile starts as soon
+//       as the flag of ITS column tile has landed, so broadcast and math overlap tile by tile.
+//
+// Reference semantics (main.cpp:1132-1194): pivot row <- P^-1 * row; every other block row i:
+// row_i -= A(i,t) * pivot_row.  We run the in-place form of Gauss-Jordan: the B = I half of
+// [A|B] is never stored; column slot t receives P^-1 (pivot row) or -A(i,t)*P^-1 (other rows),
+// which is exactly what the reference leaves in column pi(t) of B.  Work drops from the
+// reference's 3n^3 to 2n^3 flops with identical arithmetic on the non-zero terms.
+#include "common.cuh"
+#include "engine_types.h"
+#include "kernels.h"
+
+using namespace jb;
+
+namespace {
+
+constexpr int MMA_WARPS = 4;
+constexpr int STEP_THREADS = (MMA_WARPS + 1) * 32;  // + 1 TMA producer warp
+constexpr int L_BYTES = JB_LS * JB_BM * 8;          // 10240
+constexpr int R_BYTES = JB_RS * JB_BK * 8;          // 16896
+constexpr int STAGE_BYTES = L_BYTES + R_BYTES;      // 27136
+
+enum { IT_SCALE = 0, IT_ROWT = 1, IT_UPD = 2, IT_UPD_SWAPPED = 3 };
+
+struct Item {
+  int type;
+  int ct;          // column tile
+  int sub;         // 64-row sub tile inside the block row
+  int lrow0;       // first local row of the tile in W (output rows / C rows)
+  int rows_valid;  // <= JB_BM
+};
+
+struct Plan {
+  int nscale, nrowt, nupd, total;
+  int rtu;  // row tiles taking part in UPD
+};
+
+__device__ __forceinline__ Plan make_plan(const StepParams& P, const JbStepInfo& si) {
+  Plan pl;
+  pl.nscale = (si.piv_rank == P.rank) ? P.nsub * P.CT : 0;
+  pl.nrowt = (P.t_slot >= 0) ? P.CT : 0;
+  pl.rtu = (P.rloc - (P.t_slot >= 0 ? 1 : 0)) * P.nsub;
+  pl.nupd = pl.rtu * P.CT;
+  pl.total = pl.nscale + pl.nrowt + pl.nupd;
+  return pl;
+}
+
+__device__ __forceinline__ Item decode(const StepParams& P, const JbStepInfo& si, const Plan& pl,
+                                       int idx) {
+  Item it;
+  if (idx < pl.nscale) {
+    it.type = IT_SCALE;
+    it.ct = idx / P.nsub;
+    it.sub = idx - it.ct * P.nsub;
+    it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
+  } else if (idx < pl.nscale + pl.nrowt) {
+    it.type = IT_ROWT;
+    it.ct = idx - pl.nscale;
+    it.sub = 0;
+    it.lrow0 = P.t_slot * P.m;
+  } else {
+    int u = idx - pl.nscale - pl.nrowt;
+    it.ct = u / pl.rtu;
+    int rt = u - it.ct * pl.rtu;
+    int slot = rt / P.nsub;
+    it.sub = rt - slot * P.nsub;
+    if (P.t_slot >= 0 && slot >= P.t_slot) slot += 1;  // skip block row t (handled by ROWT)
+    it.lrow0 = slot * P.m + it.sub * JB_BM;
+    it.type = (si.do_swap && si.piv_rank == P.rank && slot == si.piv_slot) ? IT_UPD_SWAPPED : IT_UPD;
+  }
+  it.rows_valid = min(JB_BM, P.m - it.sub * JB_BM);
+  return it;
+}
+
+__device__ __forceinline__ double2 ld_f64x2(const double* p) {
+  return *reinterpret_cast<const double2*>(p);
+}
+__device__ __forceinline__ void st_f64x2(double* p, double x, double y) {
+  *reinterpret_cast<double2*>(p) = make_double2(x, y);
+}
+
+__global__ void __launch_bounds__(STEP_THREADS, 2)
+k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ __align__(8) uint64_t full_bar[JB_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[JB_STAGES];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+
+  if (P.ctl->singular) return;
+  const JbStepInfo si = P.stepinfo[P.t];
+  const Plan pl = make_plan(P, si);
+  if ((int)blockIdx.x >= pl.total) return;
+
+  // 128-byte aligned stage base (dynamic smem base alignment is only guaranteed to 16 B)
+  unsigned char* stage_base =
+      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem) + 127) & ~uintptr_t(127));
+
+  if (tid == 0) {
+    for (int s = 0; s < JB_STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], MMA_WARPS);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const int KC = P.Kp / JB_BK;
+  const int col_t0 = P.t * P.m, col_t1 = col_t0 + P.m;  // column slot of step t
+  double* const rowbuf_local = P.rowbuf_peers[P.rank];
+  const uint32_t* const rowflag_local = P.rowflag_peers[P.rank];
+  double* const swapbuf_local = P.swapbuf_peers[P.rank];
+  const uint32_t* const swapflag_local = P.swapflag_peers[P.rank];
+  // column tiles holding the swapped-in row's leading block A(t,t)
+  const int ctl0 = col_t0 / JB_BN, ctl1 = (col_t1 - 1) / JB_BN;
+
+  if (warp == MMA_WARPS) {
+    // =============================================================== TMA producer warp
+    if (lane == 0) {
+      tma_prefetch_desc(&M.tmW);
+      tma_prefetch_desc(&M.tmRow);
+      tma_prefetch_desc(&M.tmL);
+      tma_prefetch_desc(&M.tmInv);
+      tma_prefetch_desc(&M.tmSwap);
+      uint32_t it_cnt = 0;
+      for (int idx = blockIdx.x; idx < pl.total; idx += gridDim.x) {
+        const Item it = decode(P, si, pl, idx);
+        if (it.type == IT_ROWT) continue;
+        const int col0 = it.ct * JB_BN;
+        if (it.type != IT_SCALE) {
+          wait_flag_ge(rowflag_local + it.ct, P.row_expect);  // pivot-row tile landed
+          if (it.type == IT_UPD_SWAPPED)
+            for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c, P.tag);
+          fence_proxy_async();  // remote generic-proxy writes -> my async-proxy (TMA) reads
+        }
+        for (int c = 0; c < KC; ++c, ++it_cnt) {
+          const int s = it_cnt % JB_STAGES;
+          const uint32_t ph = (it_cnt / JB_STAGES) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          unsigned char* sb = stage_base + (size_t)s * STAGE_BYTES;
+          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          const int k0 = c * JB_BK;
+          if (it.type == IT_SCALE) {
+            tma_load_2d(sb, &M.tmInv, k0, si.piv_slot * P.Kp + it.sub * JB_BM, &full_bar[s]);
+            tma_load_2d(sb + L_BYTES, &M.tmW, col0, si.piv_slot * P.m + k0, &full_bar[s]);
+          } else if (it.type == IT_UPD) {
+            tma_load_2d(sb, &M.tmL, k0, it.lrow0, &full_bar[s]);
+            tma_load_2d(sb + L_BYTES, &M.tmRow, col0, k0, &full_bar[s]);
+          } else {
+            tma_load_2d(sb, &M.tmSwap, col_t0 + k0, it.sub * JB_BM, &full_bar[s]);
+            tma_load_2d(sb + L_BYTES, &M.tmRow, col0, k0, &full_bar[s]);
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ================================================================= MMA / copy warps
+  const int g = lane >> 2, tig = lane & 3;
+  const int wn = warp;  // 4 warps side by side along N, each 64 x 32
+  uint32_t it_cnt = 0;
+
+  for (int idx = blockIdx.x; idx < pl.total; idx += gridDim.x) {
+    const Item it = decode(P, si, pl, idx);
+    const int col0 = it.ct * JB_BN;
+
+    if (it.type == IT_ROWT) {
+      // ---- K4: swap + install the scaled pivot row as block row t
+      const int ncol = (int)min((int64_t)JB_BN, P.ldw - col0);  // multiple of 16
+      const int vec_per_row = ncol / 2;
+      double* wrow = P.W + (int64_t)it.lrow0 * P.ldw + col0;
+      if (si.do_swap) {
+        double* dst = P.swapbuf_peers[si.piv_rank] + col0;
+        for (int e = tid; e < P.m * vec_per_row; e += MMA_WARPS * 32) {
+          int r = e / vec_per_row, v = e - r * vec_per_row;
+          double2 x = ld_f64x2(wrow + (int64_t)r * P.ldw + 2 * v);
+          st_f64x2(dst + (int64_t)r * P.ldw + 2 * v, x.x, x.y);
+        }
+        __threadfence_system();
+        named_bar_sync(1, MMA_WARPS * 32);
+        if (tid == 0) st_release_sys_u32(P.swapflag_peers[si.piv_rank] + it.ct, P.tag);
+      }
+      if (lane == 0) wait_flag_ge(rowflag_local + it.ct, P.row_expect);
+      __syncwarp();
+      const double* src = rowbuf_local + col0;
+      for (int e = tid; e < P.m * vec_per_row; e += MMA_WARPS * 32) {
+        int r = e / vec_per_row, v = e - r * vec_per_row;
+        double2 x = ld_f64x2(src + (int64_t)r * P.ldw + 2 * v);
+        st_f64x2(wrow + (int64_t)r * P.ldw + 2 * v, x.x, x.y);
+      }
+      continue;
+    }
+
+    // ---- accumulator init
+    double acc[8][4][2];
+    const bool upd = (it.type != IT_SCALE);
+    if (it.type == IT_SCALE) {
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+    } else {
+      const double* cbase;
+      if (it.type == IT_UPD) {
+        cbase = P.W + (int64_t)it.lrow0 * P.ldw;
+      } else {
+        if (lane == 0) {
+          wait_flag_ge(swapflag_local + it.ct, P.tag);
+        }
+        __syncwarp();
+        cbase = swapbuf_local + (int64_t)(it.sub * JB_BM) * P.ldw;
+      }
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt) {
+        const int r = mt * 8 + g;
+        const bool rok = r < it.rows_valid;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          const int c = col0 + wn * 32 + nt * 8 + 2 * tig;
+          double2 v = make_double2(0.0, 0.0);
+          if (rok && c < P.ldw) v = ld_f64x2(cbase + (int64_t)r * P.ldw + c);
+          // column slot t starts from the identity column of B, i.e. zero for non-pivot rows
+          if (c >= col_t0 && c < col_t1) v.x = 0.0;
+          if (c + 1 >= col_t0 && c + 1 < col_t1) v.y = 0.0;
+          acc[mt][nt][0] = v.x;
+          acc[mt][nt][1] = v.y;
+        }
+      }
+    }
+
+    // ---- main loop over K = m in chunks of JB_BK, DMMA m8n8k4
+    for (int c = 0; c < KC; ++c, ++it_cnt) {
+      const int s = it_cnt % JB_STAGES;
+      const uint32_t ph = (it_cnt / JB_STAGES) & 1;
+      mbar_wait(&full_bar[s], ph);
+      const double* Ls = reinterpret_cast<const double*>(stage_base + (size_t)s * STAGE_BYTES);
+      const double* Rs = Ls + JB_LS * JB_BM;
+#pragma unroll
+      for (int kk = 0; kk < JB_BK / 4; ++kk) {
+        double a[8], b[4];
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt) {
+          double v = Ls[(mt * 8 + g) * JB_LS + kk * 4 + tig];
+          a[mt] = upd ? -v : v;
+        }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) b[nt] = Rs[(kk * 4 + tig) * JB_RS + wn * 32 + nt * 8 + g];
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[s]);
+    }
+
+    // ---- epilogue
+    if (upd) {
+      double* obase = P.W + (int64_t)it.lrow0 * P.ldw;
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt) {
+        const int r = mt * 8 + g;
+        if (r < it.rows_valid) {
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) {
+            const int c = col0 + wn * 32 + nt * 8 + 2 * tig;
+            if (c < P.ldw) st_f64x2(obase + (int64_t)r * P.ldw + c, acc[mt][nt][0], acc[mt][nt][1]);
+          }
+        }
+      }
+    } else {
+      // SCALE: column slot t of the pivot row is P^-1 itself; broadcast the tile to all ranks
+      const double* pinv = P.invbuf + (int64_t)si.piv_slot * P.Kp * P.Kp;
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt) {
+        const int r = it.sub * JB_BM + mt * 8 + g;  // row inside the pivot block
+        if (mt * 8 + g < it.rows_valid) {
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) {
+            const int c = col0 + wn * 32 + nt * 8 + 2 * tig;
+            if (c < P.ldw) {
+              double x = acc[mt][nt][0], y = acc[mt][nt][1];
+              if (c >= col_t0 && c < col_t1) x = pinv[(int64_t)r * P.Kp + (c - col_t0)];
+              if (c + 1 >= col_t0 && c + 1 < col_t1) y = pinv[(int64_t)r * P.Kp + (c + 1 - col_t0)];
+              const int64_t off = (int64_t)r * P.ldw + c;
+              if (P.rowbuf_mc) {
+                multimem_st_v2f64(P.rowbuf_mc + off, x, y);
+              } else {
+                for (int q = 0; q < P.p; ++q) st_f64x2(P.rowbuf_peers[q] + off, x, y);
+              }
+            }
+          }
+        }
+      }
+      __threadfence_system();
+      named_bar_sync(1, MMA_WARPS * 32);
+      if (tid == 0) {
+        if (P.rowflag_mc) {
+          multimem_red_release_add_u32(P.rowflag_mc + it.ct, 1u);
+        } else {
+          for (int q = 0; q < P.p; ++q) red_release_sys_add_u32(P.rowflag_peers[q] + it.ct, 1u);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+size_t jb_step_smem_bytes() { return (size_t)JB_STAGES * STAGE_BYTES + 128; }
+
+cudaError_t jb_launch_step(const StepParams& P, const StepMaps& M, int grid, cudaStream_t st) {
+  static bool configured[JB_MAX_RANKS] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev % JB_MAX_RANKS]) {
+    cudaError_t e = cudaFuncSetAttribute(k_step_fused, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)jb_step_smem_bytes());
+    if (e != cudaSuccess) return e;
+    configured[dev % JB_MAX_RANKS] = true;
+  }
+  k_step_fused<<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
+  return cudaGetLastError();
+}

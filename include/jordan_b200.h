@@ -1,0 +1,125 @@
+/* jordan_b200 — B200-native distributed dense matrix inversion (block Gauss-Jordan with block-row
+ * pivoting).  Public C ABI of libjordan_host.so (CPU-only part) and libjordan_b200.so (CUDA part).
+ *
+ * Citations "main.cpp:N" point into the reference program yusupov1alik/MPI-Jordan-crazy-acceleration
+ * whose capabilities this library reproduces.  All sizes are 64-bit (the reference overflows
+ * `int len = RpP*m*n`, main.cpp:366). */
+#ifndef JORDAN_B200_H
+#define JORDAN_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ error codes */
+#define JB_OK 0
+#define JB_ERR_CUDA (-1)
+#define JB_ERR_SINGULAR (-2) /* Jordan() return value, main.cpp:1082 */
+#define JB_ERR_NOMEM (-3)    /* main.cpp:989 */
+#define JB_ERR_ARG (-4)
+#define JB_ERR_IO (-5)
+const char* jb_last_error(void);
+
+/* ------------------------------------------------------------------ block-cyclic layout math
+ * (libjordan_host) — rows_p_process main.cpp:95-116, local_to_global 118-123,
+ * num_block_rows 124-127, find_sender 526-532. */
+int64_t jb_num_block_rows(int64_t n, int64_t m);
+int64_t jb_find_sender(int64_t Nr, int64_t p);
+int64_t jb_rows_per_process(int64_t Nr, int64_t p, int64_t k);
+int64_t jb_local_to_global_row(int64_t local_row, int64_t m, int64_t p, int64_t k);
+int64_t jb_global_to_local_row(int64_t global_row, int64_t m, int64_t p);
+int64_t jb_owner_of_row(int64_t global_row, int64_t m, int64_t p);
+int64_t jb_padded_ld(int64_t n, int64_t m); /* leading dimension used by the engine */
+
+/* ------------------------------------------------------------------ generators (f, f_i: main.cpp:47-64)
+ * ids: 1 |i-j| (default), 2 Hilbert, 3 anti-diagonal, 4 Lehmer, 5 diagonally dominant,
+ *      6 row-permuted |i-j| (exercises off-diagonal block pivots). */
+double jb_formula(int id, int64_t i, int64_t j, int64_t n);
+
+/* ------------------------------------------------------------------ text matrix I/O (libjordan_host)
+ * read_matrix main.cpp:209-282: n*n whitespace separated numbers, row-major, "%lf".
+ * Returns 0, -1 cannot open, -2 cannot read (short / garbled file). */
+int jb_read_matrix_rows(const char* path, int64_t n, int64_t row0, int64_t nrows, double* out);
+int jb_read_matrix_full(const char* path, int64_t n, double* out);
+/* print_row main.cpp:284-295: "%.2f\t" per value, "\n" per row, into a caller buffer. */
+int64_t jb_format_corner(const double* a, int64_t rows, int64_t cols, int64_t ld, char* buf,
+                         int64_t buflen);
+
+/* ------------------------------------------------------------------ CPU oracle (libjordan_host)
+ * Intended-semantics block Gauss-Jordan (SURVEY D1 fixed), emulating p ranks in one process:
+ * same pivot rule (min ||block^-1||inf, local ties -> lowest row, cross-rank ties -> highest
+ * rank), same singular test.  a: n*n row-major, overwritten; x: n*n inverse.  piv_out (optional):
+ * Nr chosen global block rows.  Returns 0 or JB_ERR_SINGULAR. */
+int jb_cpu_block_jordan(double* a, double* x, int64_t n, int64_t m, int64_t p, int32_t* piv_out);
+/* inverse_block main.cpp:746-820 restated: returns 1 if singular. */
+int jb_cpu_inverse_block(double* a, double* b, double norm, int64_t n);
+/* pivot_op main.cpp:729-735 applied as MPI's rank-ordered fold; returns winning index or -1. */
+int jb_cpu_minloc_fold(const double* norms, const int32_t* nonsing, int64_t p);
+double jb_cpu_residual(const double* a, const double* x, int64_t n);
+
+/* ------------------------------------------------------------------ GPU engine (libjordan_b200) */
+typedef struct JbEngine JbEngine;
+
+typedef struct {
+  int64_t n;       /* matrix order */
+  int32_t m;       /* block size */
+  int32_t p;       /* ranks = GPUs */
+  int32_t rank;
+  int32_t device;  /* CUDA device ordinal of this rank */
+  int32_t keep_copy; /* keep a pristine copy of A (needed for file input residual / refinement) */
+  int32_t precision; /* 0 = fp64 DMMA path, 1 = tcgen05 split-precision update + refinement */
+} JbConfig;
+
+int jb_engine_create(const JbConfig* cfg, JbEngine** out);
+void jb_engine_destroy(JbEngine* e);
+
+/* Symmetric (peer-visible) region: pivot-row buffers, swap buffer, tile flags, min-loc mailbox.
+ * Either let the engine allocate it (jb_engine_alloc_symm + IPC handle exchange) or bind memory
+ * obtained elsewhere (e.g. torch symmetric memory, which also yields an NVLS multicast alias). */
+size_t jb_engine_symm_bytes(const JbEngine* e);
+int jb_engine_alloc_symm(JbEngine* e);
+int jb_engine_bind_symm(JbEngine* e, void* const* peer_ptrs, void* multicast_ptr);
+/* which: 0 = symmetric region, 1 = matrix slab W.  handle: 64 bytes (cudaIpcMemHandle_t). */
+int jb_engine_ipc_handle(JbEngine* e, int which, void* handle64);
+int jb_engine_open_peers(JbEngine* e, int which, const void* handles /* p * 64 bytes */);
+/* Zero flags / mailboxes / step counter.  Call on all ranks, then barrier, e.g. after a singular
+ * verdict left the step epochs of the ranks inconsistent. */
+int jb_engine_reset_sync(JbEngine* e);
+
+/* matrix set-up */
+int jb_engine_fill_formula(JbEngine* e, int formula, void* stream);
+int jb_engine_upload_rows(JbEngine* e, const double* host_rows, int64_t local_row0, int64_t nrows,
+                          void* stream); /* rows are n wide; padding is handled */
+int jb_engine_finish_upload(JbEngine* e, void* stream); /* identity padding, norm, optional copy */
+int jb_engine_local_norm(JbEngine* e, double* out);     /* local ||A||inf (synchronises) */
+int jb_engine_set_norm(JbEngine* e, double global_norm); /* after a MAX reduction over the ranks */
+
+/* the timed region: enqueue all Nr elimination steps + final column un-permutation */
+int jb_engine_invert(JbEngine* e, void* stream);
+/* synchronise and fetch the verdict: JB_OK or JB_ERR_SINGULAR */
+int jb_engine_status(JbEngine* e, void* stream);
+int jb_engine_pivots(JbEngine* e, int32_t* piv_out /* Nr */);
+int64_t jb_engine_launch_count(const JbEngine* e); /* kernels launched by this engine so far */
+
+/* results */
+void* jb_engine_w_ptr(JbEngine* e);
+int64_t jb_engine_ldw(const JbEngine* e);
+int64_t jb_engine_local_rows(const JbEngine* e);
+int jb_engine_download(JbEngine* e, int which /*0 = X (W), 1 = kept copy of A*/, int64_t local_row0,
+                       int64_t nrows, int64_t col0, int64_t ncols, double* host, int64_t ldh);
+/* local max_i sum_j |(A X - I)_ij| over this rank's rows; formula < 0 -> use the kept copy. */
+int jb_engine_residual(JbEngine* e, int formula, double* out_local, void* stream);
+/* one Newton step X <- X + X (I - A X) in fp64 (K7). Collective: barrier before and after. */
+int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
+
+/* stand-alone kernels for tests / tools */
+int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
+                     double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
+int jb_dgemm_peak(int64_t n, int iters, double* tflops_out); /* cuBLAS-free DMMA roofline probe */
+
+#ifdef __cplusplus
+}
+#endif
+#endif
