@@ -17,6 +17,7 @@
 // distributed shared memory (m = 256 -> CS = 4) per candidate.  Extra CTAs appended to the grid
 // copy block-column t into the contiguous L panel used by the trailing update.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "engine_types.h"
 #include "kernels.h"
@@ -97,6 +98,289 @@ __device__ void minloc_exchange(const K1Params& P, int best_slot, double best_no
   P.stepinfo[P.t] = si;
 }
 
+
+// Executed by ONE thread per candidate: publish the candidate's verdict; the last arriving
+// candidate performs the local arg-min and the cross-GPU min-loc exchange.
+__device__ void finish_candidate(const K1Params& P, bool dummy, int slot, double mynorm,
+                                 bool singular) {
+  if (!dummy) {
+    P.normbuf[slot] = mynorm;
+    P.okbuf[slot] = singular ? 0 : 1;
+    __threadfence();
+  }
+  const unsigned want = dummy ? 0u : (unsigned)(P.ncand - 1);
+  unsigned ticket = dummy ? 0u : atomicAdd(&P.ctl->ticket, 1u);
+  if (ticket != want) return;
+  P.ctl->ticket = 0;
+  __threadfence();
+  int best_slot = P.s0, have = 0;
+  double best_norm = 0.0;
+  for (int s = P.s0; s < P.s0 + P.ncand; ++s) {  // strict <, first wins (main.cpp:1051-1064)
+    if (((volatile int*)P.okbuf)[s]) {
+      double v = ((volatile double*)P.normbuf)[s];
+      if (!have || v < best_norm) {
+        best_norm = v;
+        best_slot = s;
+        have = 1;
+      }
+    }
+  }
+  minloc_exchange(P, best_slot, best_norm, have);
+}
+
+// Lbuf[r][k] = W[r][t*m + k] for every local row r (contiguous K-major panel for TMA).
+__device__ void panel_copy(const K1Params& P, int cta, int nctas) {
+  const int tid = threadIdx.x;
+  const int wpb = blockDim.x >> 5;
+  const int64_t rows = (int64_t)P.rloc * P.m;
+  const int nwarps = nctas * wpb;
+  const int wid = cta * wpb + (tid >> 5);
+  const double* src = P.W + (int64_t)P.t * P.m;
+  for (int64_t r = wid; r < rows; r += nwarps)
+    for (int k = tid & 31; k < P.m; k += 32) P.Lbuf[r * P.Kp + k] = src[r * P.ldw + k];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fast path: the whole (padded) MB x MB block lives in REGISTERS.  Warp w owns rows
+// {w + NW*i}, lane l owns columns {l + 32*j}; per elimination column only the pivot row (through
+// shared memory / DSMEM) and one candidate per warp are exchanged: 2 barriers per column, no
+// shared-memory traffic for the rank-1 update itself.
+// ---------------------------------------------------------------------------------------------
+struct FCand {
+  double val;
+  int lpos;   // logical position (tie-break: lowest wins), -1 = none
+  int phys;   // physical row of the block
+};
+
+template <int MB, int NW, int CS>
+__global__ void __launch_bounds__(NW * 32, 1) k1_fast(const K1Params P) {
+  constexpr int ROWS_CTA = MB / CS;        // rows of the block held by this CTA
+  constexpr int RPT = ROWS_CTA / NW;       // rows per thread
+  constexpr int CPT = MB / 32;             // columns per thread
+  constexpr int NC = CS * NW;              // candidates per column
+  static_assert(RPT >= 1 && CPT >= 1, "bad tiling");
+  __shared__ FCand cand[2][NC];
+  __shared__ double prow[2][MB];
+  __shared__ int rowof[MB];
+  __shared__ int pos[MB];
+  __shared__ double s_red[NW];
+  __shared__ double s_cl[CS];
+
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  const int m = P.m;
+  int crank = 0;
+  if constexpr (CS > 1) crank = (int)cg::this_cluster().block_rank();
+  const int group = blockIdx.x / CS;
+  if (P.ctl->singular) return;
+  if (group >= P.ngroups) {
+    panel_copy(P, blockIdx.x - P.ngroups * CS, gridDim.x - P.ngroups * CS);
+    return;
+  }
+  const bool dummy = (P.ncand == 0);
+  const int slot = P.s0 + group;
+  const double norm_a = P.ctl->norm_a;
+  const double thr = JB_EPS * norm_a;
+  const int row_base = crank * ROWS_CTA;
+
+  double a[RPT][CPT];
+  if (!dummy) {
+    const double* src = P.W + (int64_t)slot * m * P.ldw + (int64_t)P.t * m;
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const int r = row_base + w + NW * i;
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        const int c = lane + 32 * j;
+        a[i][j] = (r < m && c < m) ? src[(int64_t)r * P.ldw + c] : ((r == c) ? 1.0 : 0.0);
+      }
+    }
+    for (int i = tid; i < MB; i += NW * 32) {
+      rowof[i] = i;
+      pos[i] = i;
+    }
+  }
+  group_sync<CS>();
+
+  bool singular = dummy ? true : (fabs(norm_a) < JB_EPS);
+  if (!singular) {
+#pragma unroll
+    for (int cc = 0; cc < CPT; ++cc) {
+      for (int kk = 0; kk < 32; ++kk) {
+        const int k = cc * 32 + kk;
+        if (k >= m) break;  // padding columns are decoupled from the real block
+        const int par = k & 1;
+        // (1) one candidate per warp: the lane owning column k scans its rows
+        if (lane == kk) {
+          double bv = -1.0;
+          int bl = -1, bp = -1;
+#pragma unroll
+          for (int i = 0; i < RPT; ++i) {
+            const int r = row_base + w + NW * i;
+            const int lp = pos[r];
+            const double v = fabs(a[i][cc]);
+            if (lp >= k && (v > bv || (v == bv && lp < bl))) {
+              bv = v;
+              bl = lp;
+              bp = r;
+            }
+          }
+          FCand c;
+          c.val = bv;
+          c.lpos = bl;
+          c.phys = bp;
+          if constexpr (CS == 1) {
+            cand[par][w] = c;
+          } else {
+            cg::cluster_group cl = cg::this_cluster();
+#pragma unroll
+            for (int q = 0; q < CS; ++q) cl.map_shared_rank(&cand[0][0], q)[par * NC + crank * NW + w] = c;
+          }
+        }
+        group_sync<CS>();
+        // (2) every warp reduces the NC candidates: max |value|, ties -> lowest logical position
+        double bv = -1.0;
+        int bl = -1, bp = -1;
+        for (int q = lane; q < NC; q += 32) {
+          const FCand c = cand[par][q];
+          if (c.lpos >= 0 && (bl < 0 || c.val > bv || (c.val == bv && c.lpos < bl))) {
+            bv = c.val;
+            bl = c.lpos;
+            bp = c.phys;
+          }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          const double ov = __shfl_xor_sync(0xffffffffu, bv, off);
+          const int ol = __shfl_xor_sync(0xffffffffu, bl, off);
+          const int op = __shfl_xor_sync(0xffffffffu, bp, off);
+          if (ol >= 0 && (bl < 0 || ov > bv || (ov == bv && ol < bl))) {
+            bv = ov;
+            bl = ol;
+            bp = op;
+          }
+        }
+        if (bl < 0 || bv < thr) {  // |a_kk| < EPS * ||A||  (main.cpp:782); uniform everywhere
+          singular = true;
+          break;
+        }
+        const int pr = bp;                     // physical pivot row
+        const int prl = pr - row_base;         // local row index if this CTA holds it
+        const bool cta_owns = (prl >= 0 && prl < ROWS_CTA);
+        const bool warp_owns = cta_owns && ((prl % NW) == w);
+        const int ip = prl / NW;               // register row of the pivot (owner warp only)
+        // multipliers f_i = a[i][k] of my rows come from the lane owning column k
+        double f[RPT];
+#pragma unroll
+        for (int i = 0; i < RPT; ++i) f[i] = __shfl_sync(0xffffffffu, a[i][cc], kk);
+        if (warp_owns) {
+          double pv[CPT];
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            double v = 0.0;
+#pragma unroll
+            for (int i = 0; i < RPT; ++i) v = (i == ip) ? a[i][j] : v;
+            pv[j] = v;
+          }
+          const double dinv = 1.0 / __shfl_sync(0xffffffffu, pv[cc], kk);
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            const int c = lane + 32 * j;
+            const double v = (c == k) ? dinv : pv[j] * dinv;
+            if constexpr (CS == 1) {
+              prow[par][c] = v;
+            } else {
+              cg::cluster_group cl = cg::this_cluster();
+#pragma unroll
+              for (int q = 0; q < CS; ++q) cl.map_shared_rank(&prow[0][0], q)[par * MB + c] = v;
+            }
+          }
+        }
+        if (tid == 0) {  // logical row interchange k <-> bl (same bookkeeping on every CTA)
+          const int other = rowof[k];
+          rowof[k] = pr;
+          rowof[bl] = other;
+          pos[pr] = k;
+          pos[other] = bl;
+        }
+        group_sync<CS>();
+        // (3) rank-1 update of my register tile
+        double pj[CPT];
+#pragma unroll
+        for (int j = 0; j < CPT; ++j) pj[j] = prow[par][lane + 32 * j];
+#pragma unroll
+        for (int i = 0; i < RPT; ++i) {
+          const bool is_piv = warp_owns && (i == ip);
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            double base = a[i][j];
+            if (j == cc && lane == kk) base = 0.0;  // column slot k starts from the identity column
+            a[i][j] = is_piv ? pj[j] : fma(-f[i], pj[j], base);
+          }
+        }
+      }
+      if (singular) break;
+    }
+  }
+
+  // ---- write-out: Inv[logical i][rowof[kk]] = S[phys(i)][kk]; norm = max abs row sum
+  double mynorm = 0.0;
+  if (!singular) {
+    double* inv = P.invbuf + (int64_t)slot * P.Kp * P.Kp;
+    double wmax = 0.0;
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      const int r = row_base + w + NW * i;
+      const int li = pos[r];
+      double sum = 0.0;
+#pragma unroll
+      for (int j = 0; j < CPT; ++j) {
+        const int c = lane + 32 * j;
+        const int oc = rowof[c];
+        if (li < m && oc < m) {
+          inv[(int64_t)li * P.Kp + oc] = a[i][j];
+          sum += fabs(a[i][j]);
+        }
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+      wmax = fmax(wmax, sum);
+    }
+    if (lane == 0) s_red[w] = wmax;
+    __syncthreads();
+    if (tid == 0)
+      for (int q = 0; q < NW; ++q) mynorm = fmax(mynorm, s_red[q]);
+  }
+  if constexpr (CS > 1) {
+    cg::cluster_group cl = cg::this_cluster();
+    if (tid == 0) cl.map_shared_rank(&s_cl[0], 0)[crank] = mynorm;
+    cl.sync();
+    if (crank == 0 && tid == 0) {
+      mynorm = 0.0;
+      for (int q = 0; q < CS; ++q) mynorm = fmax(mynorm, s_cl[q]);
+    }
+  }
+  if (crank != 0 || tid != 0) return;
+  finish_candidate(P, dummy, slot, mynorm, singular);
+}
+
+template <int MB, int NW, int CS>
+cudaError_t launch_k1_fast(const K1Params& P, int panel_ctas, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  panel_ctas = (panel_ctas + CS - 1) / CS * CS;
+  cfg.gridDim = dim3((unsigned)(P.ngroups * CS + panel_ctas));
+  cfg.blockDim = dim3(NW * 32);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (CS > 1) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, k1_fast<MB, NW, CS>, P);
+}
+
 template <int CS>
 __global__ void __launch_bounds__(K1_THREADS, 1) k1_pivot_search(const K1Params P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -110,13 +394,7 @@ __global__ void __launch_bounds__(K1_THREADS, 1) k1_pivot_search(const K1Params 
 
   // ---------------------------------------------------------------- panel-copy CTAs
   if (group >= P.ngroups) {
-    // Lbuf[r][k] = W[r][t*m + k] for every local row r (contiguous K-major panel for TMA).
-    const int64_t rows = (int64_t)P.rloc * m;
-    const int nwarps = (int)(gridDim.x - P.ngroups * CS) * (K1_THREADS / 32);
-    const int wid = (int)(blockIdx.x - P.ngroups * CS) * (K1_THREADS / 32) + (tid >> 5);
-    const double* src = P.W + (int64_t)P.t * m;
-    for (int64_t r = wid; r < rows; r += nwarps)
-      for (int k = tid & 31; k < m; k += 32) P.Lbuf[r * P.Kp + k] = src[r * P.ldw + k];
+    panel_copy(P, blockIdx.x - P.ngroups * CS, gridDim.x - P.ngroups * CS);
     return;
   }
 
@@ -299,30 +577,7 @@ __global__ void __launch_bounds__(K1_THREADS, 1) k1_pivot_search(const K1Params 
   }
   if (crank != 0 || tid != 0) return;
 
-  // ---------------------------------------------------------------- local arg-min + min-loc
-  if (!dummy) {
-    P.normbuf[slot] = mynorm;
-    P.okbuf[slot] = singular ? 0 : 1;
-    __threadfence();
-  }
-  const unsigned want = dummy ? 0u : (unsigned)(P.ncand - 1);
-  unsigned ticket = dummy ? 0u : atomicAdd(&P.ctl->ticket, 1u);
-  if (ticket != want) return;
-  P.ctl->ticket = 0;
-  __threadfence();
-  int best_slot = P.s0, have = 0;
-  double best_norm = 0.0;
-  for (int s = P.s0; s < P.s0 + P.ncand; ++s) {  // strict <, first wins (main.cpp:1051-1064)
-    if (((volatile int*)P.okbuf)[s]) {
-      double v = ((volatile double*)P.normbuf)[s];
-      if (!have || v < best_norm) {
-        best_norm = v;
-        best_slot = s;
-        have = 1;
-      }
-    }
-  }
-  minloc_exchange(P, best_slot, best_norm, have);
+  finish_candidate(P, dummy, slot, mynorm, singular);
 }
 
 size_t k1_smem_bytes(int m, int CS) {
@@ -374,6 +629,13 @@ int jb_k1_cluster_size(int m) {
 }
 
 cudaError_t jb_launch_k1(const K1Params& P, int panel_ctas, cudaStream_t st) {
+  static const bool generic_only = getenv("JB_K1_GENERIC") != nullptr;
+  if (!generic_only) {
+    if (P.m <= 32) return launch_k1_fast<32, 8, 1>(P, panel_ctas, st);
+    if (P.m <= 64) return launch_k1_fast<64, 16, 1>(P, panel_ctas, st);
+    if (P.m <= 128) return launch_k1_fast<128, 16, 1>(P, panel_ctas, st);
+    if (P.m <= 256) return launch_k1_fast<256, 16, 4>(P, panel_ctas, st);
+  }
   switch (jb_k1_cluster_size(P.m)) {
     case 1: return launch_k1<1>(P, panel_ctas, st);
     case 2: return launch_k1<2>(P, panel_ctas, st);

@@ -3,6 +3,7 @@
 // stream with no host synchronisation: the pivot choice of every step stays in device memory.
 // This is the B200 replacement of solve()/Jordan() (main.cpp:343-519, 953-1204).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <vector>
@@ -90,6 +91,10 @@ struct JbEngine {
   uint32_t gstep = 0;  // global step counter (same on every rank)
   int64_t launches = 0;
   bool norm_set = false;
+  // optional per-kernel timing (JB_TIME_KERNELS=1 or jb_engine_set_profiling)
+  bool profile = false;
+  std::vector<cudaEvent_t> ev;
+  double prof_k1_ms = 0, prof_step_ms = 0, prof_tail_ms = 0;
 };
 
 namespace {
@@ -180,6 +185,7 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   e->off_mail = off; off += align_up(2 * JB_MAX_RANKS * sizeof(JbMail), 256);
   e->symm_bytes = align_up(off, 4096);
   e->W_peers[e->rank] = e->W;
+  if (getenv("JB_TIME_KERNELS")) e->profile = true;
   *out = e;
   return JB_OK;
 }
@@ -386,7 +392,13 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   const int grid = 2 * e->sm_count;
   const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
 
+  if (e->profile && e->ev.size() < (size_t)(2 * e->Nr + 2)) {
+    size_t old = e->ev.size();
+    e->ev.resize((size_t)(2 * e->Nr + 2));
+    for (size_t i = old; i < e->ev.size(); ++i) JB_CHECK(cudaEventCreate(&e->ev[i]));
+  }
   for (int64_t t = 0; t < e->Nr; ++t) {
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t], st));
     const uint32_t g = e->gstep++;
     const int par = g & 1;
     // ---- K1: candidates are local block rows with global index >= t (main.cpp:1028)
@@ -397,6 +409,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     K.ngroups = std::max(K.ncand, 1);
     K.tag = g + 1;
     JB_CHECK(jb_launch_k1(K, panel_ctas, st));
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t + 1], st));
     // ---- fused scale + broadcast + swap + trailing update
     S.t = (int)t;
     S.t_slot = (t % e->p == e->rank) ? (int)(t / e->p) : -1;
@@ -411,8 +424,36 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     JB_CHECK(jb_launch_step(S, e->maps[par], grid, st));
     e->launches += 2;
   }
+  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * e->Nr], st));
   JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
   e->launches += (e->rows_loc > 0);
+  if (e->profile) {
+    JB_CHECK(cudaEventRecord(e->ev[2 * e->Nr + 1], st));
+    JB_CHECK(cudaStreamSynchronize(st));
+    e->prof_k1_ms = e->prof_step_ms = 0;
+    for (int64_t t = 0; t < e->Nr; ++t) {
+      float a = 0, b = 0;
+      JB_CHECK(cudaEventElapsedTime(&a, e->ev[2 * t], e->ev[2 * t + 1]));
+      JB_CHECK(cudaEventElapsedTime(&b, e->ev[2 * t + 1], e->ev[2 * t + 2]));
+      e->prof_k1_ms += a;
+      e->prof_step_ms += b;
+    }
+    float c = 0;
+    JB_CHECK(cudaEventElapsedTime(&c, e->ev[2 * e->Nr], e->ev[2 * e->Nr + 1]));
+    e->prof_tail_ms = c;
+  }
+  return JB_OK;
+}
+
+int jb_engine_set_profiling(JbEngine* e, int on) {
+  e->profile = on != 0;
+  return JB_OK;
+}
+
+int jb_engine_phase_times(JbEngine* e, double* k1_ms, double* step_ms, double* tail_ms) {
+  *k1_ms = e->prof_k1_ms;
+  *step_ms = e->prof_step_ms;
+  *tail_ms = e->prof_tail_ms;
   return JB_OK;
 }
 
@@ -422,7 +463,7 @@ int jb_engine_status(JbEngine* e, void* stream) {
   JbCtl c;
   JB_CHECK(cudaMemcpy(&c, e->ctl, sizeof(c), cudaMemcpyDeviceToHost));
   if (c.singular) {
-    jb_set_error("singular matrix");  // main.cpp:438
+    jb_set_error("singular matrix (step %d)", c.singular_step);  // main.cpp:438
     return JB_ERR_SINGULAR;
   }
   return JB_OK;

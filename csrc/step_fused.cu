@@ -7,7 +7,7 @@
 //   ROWT items (owner of block row t): push the old row t into the pivot owner's swap buffer over
 //       NVLink (the block-row swap of main.cpp:1100-1131 done with peer stores instead of
 //       MPI_Send/Recv), then replace row t by the scaled pivot row.
-//   UPD  items (every rank): C(i,j) -= A(i,t) * R_j for all local rows, DMMA m8n8k4, operands fed by
+//   UPD  items (every rank): C(i,j) += A(i,t) * (-R_j) for all local rows, DMMA m8n8k4, operands fed by
 //       TMA (cp.async.bulk.tensor) through a 4-stage mbarrier ring.  A consumer tile starts as soon
 //       as the flag of ITS column tile has landed, so broadcast and math overlap tile by tile.
 //
@@ -91,7 +91,7 @@ __device__ __forceinline__ void st_f64x2(double* p, double x, double y) {
 
 __global__ void __launch_bounds__(STEP_THREADS, 2)
 k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
-  extern __shared__ __align__(128) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t full_bar[JB_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[JB_STAGES];
 
@@ -104,9 +104,12 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   const Plan pl = make_plan(P, si);
   if ((int)blockIdx.x >= pl.total) return;
 
-  // 128-byte aligned stage base (dynamic smem base alignment is only guaranteed to 16 B)
+#ifdef JB_DBG_GENERIC
   unsigned char* stage_base =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem) + 127) & ~uintptr_t(127));
+#else
+  unsigned char* const stage_base = smem;  // TMA destinations need 128-byte alignment
+#endif
 
   if (tid == 0) {
     for (int s = 0; s < JB_STAGES; ++s) {
@@ -199,7 +202,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
       for (int e = tid; e < P.m * vec_per_row; e += MMA_WARPS * 32) {
         int r = e / vec_per_row, v = e - r * vec_per_row;
         double2 x = ld_f64x2(src + (int64_t)r * P.ldw + 2 * v);
-        st_f64x2(wrow + (int64_t)r * P.ldw + 2 * v, x.x, x.y);
+        st_f64x2(wrow + (int64_t)r * P.ldw + 2 * v, -x.x, -x.y);  // rowbuf holds -R
       }
       continue;
     }
@@ -253,8 +256,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         double a[8], b[4];
 #pragma unroll
         for (int mt = 0; mt < 8; ++mt) {
-          double v = Ls[(mt * 8 + g) * JB_LS + kk * 4 + tig];
-          a[mt] = upd ? -v : v;
+          a[mt] = Ls[(mt * 8 + g) * JB_LS + kk * 4 + tig];
         }
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) b[nt] = Rs[(kk * 4 + tig) * JB_RS + wn * 32 + nt * 8 + g];
@@ -263,6 +265,11 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
 #pragma unroll
           for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
       }
+      // Stage release is a WAR hazard ACROSS PROXIES: our LDS reads (generic proxy) must be ordered
+      // before the producer's next TMA write (async proxy) into the same stage.  The mbarrier
+      // arrive alone only orders the generic proxy (ptxas even hoists it above the consuming
+      // DMMAs), which showed up as sporadically corrupted tiles once W exceeded L2.
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[s]);
     }
@@ -292,13 +299,15 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           for (int nt = 0; nt < 4; ++nt) {
             const int c = col0 + wn * 32 + nt * 8 + 2 * tig;
             if (c < P.ldw) {
-              double x = acc[mt][nt][0], y = acc[mt][nt][1];
-              if (c >= col_t0 && c < col_t1) x = pinv[(int64_t)r * P.Kp + (c - col_t0)];
-              if (c + 1 >= col_t0 && c + 1 < col_t1) y = pinv[(int64_t)r * P.Kp + (c + 1 - col_t0)];
+              // the buffer holds -R so the update is a plain accumulate C += L * (-R)
+              double x = -acc[mt][nt][0], y = -acc[mt][nt][1];
+              if (c >= col_t0 && c < col_t1) x = -pinv[(int64_t)r * P.Kp + (c - col_t0)];
+              if (c + 1 >= col_t0 && c + 1 < col_t1) y = -pinv[(int64_t)r * P.Kp + (c + 1 - col_t0)];
               const int64_t off = (int64_t)r * P.ldw + c;
               if (P.rowbuf_mc) {
                 multimem_st_v2f64(P.rowbuf_mc + off, x, y);
               } else {
+#pragma unroll 1
                 for (int q = 0; q < P.p; ++q) st_f64x2(P.rowbuf_peers[q] + off, x, y);
               }
             }
@@ -311,6 +320,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         if (P.rowflag_mc) {
           multimem_red_release_add_u32(P.rowflag_mc + it.ct, 1u);
         } else {
+#pragma unroll 1
           for (int q = 0; q < P.p; ++q) red_release_sys_add_u32(P.rowflag_peers[q] + it.ct, 1u);
         }
       }
@@ -320,7 +330,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
 
 }  // namespace
 
-size_t jb_step_smem_bytes() { return (size_t)JB_STAGES * STAGE_BYTES + 128; }
+size_t jb_step_smem_bytes() { return (size_t)JB_STAGES * STAGE_BYTES; }
 
 cudaError_t jb_launch_step(const StepParams& P, const StepMaps& M, int grid, cudaStream_t st) {
   static bool configured[JB_MAX_RANKS] = {false};

@@ -102,6 +102,9 @@ int jb_engine_invert(JbEngine* e, void* stream);
 int jb_engine_status(JbEngine* e, void* stream);
 int jb_engine_pivots(JbEngine* e, int32_t* piv_out /* Nr */);
 int64_t jb_engine_launch_count(const JbEngine* e); /* kernels launched by this engine so far */
+/* per-kernel CUDA-event timing of the last jb_engine_invert (adds a stream sync; off by default) */
+int jb_engine_set_profiling(JbEngine* e, int on);
+int jb_engine_phase_times(JbEngine* e, double* k1_ms, double* step_ms, double* tail_ms);
 
 /* results */
 void* jb_engine_w_ptr(JbEngine* e);
@@ -117,7 +120,6 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
 /* stand-alone kernels for tests / tools */
 int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
                      double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
-int jb_dgemm_peak(int64_t n, int iters, double* tflops_out); /* cuBLAS-free DMMA roofline probe */
 
 #ifdef __cplusplus
 }

@@ -95,6 +95,8 @@ def _declare_cuda(lib) -> None:
         "jb_engine_status": (C.c_int, [vp, vp]),
         "jb_engine_pivots": (C.c_int, [vp, vp]),
         "jb_engine_launch_count": (i64, [vp]),
+        "jb_engine_set_profiling": (C.c_int, [vp, C.c_int]),
+        "jb_engine_phase_times": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "jb_engine_w_ptr": (vp, [vp]),
         "jb_engine_ldw": (i64, [vp]),
         "jb_engine_local_rows": (i64, [vp]),
@@ -138,7 +140,7 @@ def cuda():
     global _cuda
     if _cuda is None:
         _ensure_built("cuda")
-        path = _LIBDIR / "libjordan_b200.so"
+        path = Path(os.environ.get("JB_CUDA_LIB", str(_LIBDIR / "libjordan_b200.so")))
         try:
             _cuda = C.CDLL(str(path))
         except OSError as exc:  # pragma: no cover

@@ -258,6 +258,16 @@ class JordanSolver:
             _native.check(self.lib.jb_engine_refine_phase(self._h, fid, 1, self._stream()))
         torch.cuda.synchronize()
 
+    def set_profiling(self, on: bool = True) -> None:
+        _native.check(self.lib.jb_engine_set_profiling(self._h, int(on)))
+
+    def phase_times(self) -> dict:
+        """Device time (ms) of the last inversion split into K1 (pivot search + min-loc), the fused
+        step kernels, and the final un-permutation.  Needs ``set_profiling(True)``."""
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        _native.check(self.lib.jb_engine_phase_times(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"k1_ms": a.value, "step_ms": b.value, "tail_ms": c.value}
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.jb_engine_launch_count(self._h))

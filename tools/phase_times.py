@@ -1,0 +1,32 @@
+"""Per-phase device times of one inversion: K1 (pivot search + min-loc) vs fused step kernels.
+usage: python tools/phase_times.py n m [n m ...]"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from mpi_jordan_crazy_acceleration_b200.models.jordan import JordanSolver, _SingleComm  # noqa: E402
+
+
+def main():
+    args = [int(x) for x in sys.argv[1:]] or [8192, 128]
+    for n, m in zip(args[0::2], args[1::2]):
+        s = JordanSolver(n, m, comm=_SingleComm())
+        s.set_profiling(True)
+        for _ in range(2):
+            s.fill_formula(1)
+            sec = s.invert()
+        pt = s.phase_times()
+        tf = 2.0 * n ** 3 / sec / 1e12
+        step_tf = 2.0 * n ** 3 / (pt["step_ms"] * 1e-3) / 1e12
+        print(json.dumps({"n": n, "m": m, "seconds": sec, "tflops": tf, "step_only_tflops": step_tf,
+                          "k1_us_per_step": pt["k1_ms"] * 1e3 / s.layout.Nr,
+                          "step_us_per_step": pt["step_ms"] * 1e3 / s.layout.Nr, **pt}), flush=True)
+        s.close()
+        torch.cuda.synchronize()
+
+
+if __name__ == "__main__":
+    main()
