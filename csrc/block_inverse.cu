@@ -209,23 +209,25 @@ __global__ void __launch_bounds__(NW * 32, 1) k1_fast(const K1Params P) {
         const int k = cc * 32 + kk;
         if (k >= m) break;  // padding columns are decoupled from the real block
         const int par = k & 1;
-        // (1) one candidate per warp: the lane owning column k scans its rows
+        // (1) one candidate per warp: the lane owning column k scans its rows.  |value| is compared
+        //     through its bit pattern (non-negative doubles order like unsigned integers), which
+        //     keeps the FP64 pipe latency out of the dependent chain.
         if (lane == kk) {
-          double bv = -1.0;
+          unsigned long long bkey = 0ull;
           int bl = -1, bp = -1;
 #pragma unroll
           for (int i = 0; i < RPT; ++i) {
             const int r = row_base + w + NW * i;
             const int lp = pos[r];
-            const double v = fabs(a[i][cc]);
-            if (lp >= k && (v > bv || (v == bv && lp < bl))) {
-              bv = v;
+            const unsigned long long key = (unsigned long long)__double_as_longlong(fabs(a[i][cc]));
+            if (lp >= k && (bl < 0 || key > bkey || (key == bkey && lp < bl))) {
+              bkey = key;
               bl = lp;
               bp = r;
             }
           }
           FCand c;
-          c.val = bv;
+          c.val = __longlong_as_double((long long)bkey);
           c.lpos = bl;
           c.phys = bp;
           if constexpr (CS == 1) {
@@ -237,28 +239,34 @@ __global__ void __launch_bounds__(NW * 32, 1) k1_fast(const K1Params P) {
           }
         }
         group_sync<CS>();
-        // (2) every warp reduces the NC candidates: max |value|, ties -> lowest logical position
-        double bv = -1.0;
+        // (2) every warp reduces the NC candidates with four REDUX ops: max |value| (high word, low
+        //     word), then lowest logical position among the ties, then fetch the winner's row.
+        unsigned long long mykey = 0ull;
         int bl = -1, bp = -1;
         for (int q = lane; q < NC; q += 32) {
           const FCand c = cand[par][q];
-          if (c.lpos >= 0 && (bl < 0 || c.val > bv || (c.val == bv && c.lpos < bl))) {
-            bv = c.val;
+          const unsigned long long key = (unsigned long long)__double_as_longlong(c.val);
+          if (c.lpos >= 0 && (bl < 0 || key > mykey || (key == mykey && c.lpos < bl))) {
+            mykey = key;
             bl = c.lpos;
             bp = c.phys;
           }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-          const double ov = __shfl_xor_sync(0xffffffffu, bv, off);
-          const int ol = __shfl_xor_sync(0xffffffffu, bl, off);
-          const int op = __shfl_xor_sync(0xffffffffu, bp, off);
-          if (ol >= 0 && (bl < 0 || ov > bv || (ov == bv && ol < bl))) {
-            bv = ov;
-            bl = ol;
-            bp = op;
-          }
+        {
+          const bool valid = bl >= 0;
+          const unsigned hi = valid ? (unsigned)(mykey >> 32) : 0u;
+          const unsigned lo = valid ? (unsigned)mykey : 0u;
+          const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+          const unsigned ml = __reduce_max_sync(0xffffffffu, (valid && hi == mh) ? lo : 0u);
+          const bool match = valid && hi == mh && lo == ml;
+          const unsigned mlp = __reduce_min_sync(0xffffffffu, match ? (unsigned)bl : 0xffffffffu);
+          const bool win = match && (unsigned)bl == mlp;
+          const unsigned wp = __reduce_max_sync(0xffffffffu, win ? (unsigned)bp : 0u);
+          mykey = ((unsigned long long)mh << 32) | ml;
+          bl = (mlp == 0xffffffffu) ? -1 : (int)mlp;
+          bp = (int)wp;
         }
+        const double bv = __longlong_as_double((long long)mykey);
         if (bl < 0 || bv < thr) {  // |a_kk| < EPS * ||A||  (main.cpp:782); uniform everywhere
           singular = true;
           break;
