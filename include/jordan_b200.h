@@ -120,6 +120,16 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
 /* stand-alone kernels for tests / tools */
 int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
                      double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
+/* Same operation for callers that must not allocate (all device memory already handed to a pool,
+ * or no room for cudaMalloc's device-wide synchronisation).  No counterpart in the reference.
+ * Staging lives in a fixed ~4 MiB device array inside the library (resident on every GPU that
+ * loads it): accepted only if nblocks * Kp * Kp <= 524288 doubles (Kp = m rounded up to 16) and
+ * m <= 256, otherwise JB_ERR_ARG.  Calls no cudaMalloc/cudaFree.  Asynchronous on `stream`
+ * (synchronise before reading the outputs).  All calls on a device share the array: calls that
+ * overlap on the GPU race.  The first call on each device resolves the array's address; make it
+ * during initialisation, before any stream capture begins. */
+int jb_block_inverse_noalloc(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
+                             double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
 
 #ifdef __cplusplus
 }
