@@ -1,0 +1,132 @@
+"""Run the UNMODIFIED reference (baseline/_ref/a.out = /root/reference/main.cpp built as shipped
+against the in-tree MPI shim) through its own command line and parse its report.
+
+The reference is a CPU/MPI program: "N GPUs" maps to N MPI ranks on the host CPUs.  Its timed
+region is Jordan() only (main.cpp:427-450); the residual phase that follows is untimed and, for
+block sizes not divisible by 3, pathologically slow, so the process group is
+stopped as soon as the `glob_time:` line has been read (rank 0's stdout is line buffered).
+"""
+from __future__ import annotations
+
+import json
+import os
+import re
+import signal
+import subprocess
+import sys
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+MPIRUN = os.path.join(ROOT, "bin", "jb_mpirun")
+
+
+def ensure_built() -> str | None:
+    exe = os.path.join(REF_DIR, "a.out")
+    if os.path.exists(exe) and os.path.exists(MPIRUN):
+        return None
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    r = subprocess.run(["sh", os.path.join(HERE, "build_reference.sh")], capture_output=True, text=True,
+                       env=env, cwd=ROOT)
+    if r.returncode != 0 or not os.path.exists(exe):
+        return ("reference build failed: " + (r.stdout + r.stderr).strip().replace("\n", " | "))[:300]
+    return None
+
+
+def run_once(n: int, m: int, ranks: int, timeout_s: float, want_residual: bool = False,
+             exe: str = "a.out", extra: list[str] | None = None) -> dict:
+    """Returns {"glob_time": s, "residual": r|None, "rc": rc|None, "timed_out": bool, "stdout": str}."""
+    cmd = [MPIRUN, "-np", str(ranks), os.path.join(REF_DIR, exe), str(n), str(m)] + (extra or [])
+    t0 = time.time()
+    proc = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                            start_new_session=True)
+    out_lines: list[str] = []
+    glob_time = None
+    residual = None
+    timed_out = False
+    import selectors
+
+    sel = selectors.DefaultSelector()
+    sel.register(proc.stdout, selectors.EVENT_READ)
+    try:
+        while True:
+            left = timeout_s - (time.time() - t0)
+            if left <= 0:
+                timed_out = True
+                break
+            if not sel.select(timeout=min(left, 1.0)):
+                if proc.poll() is not None:
+                    break
+                continue
+            line = proc.stdout.readline()
+            if not line:
+                break
+            out_lines.append(line)
+            mt = re.match(r"glob_time: ([0-9.eE+-]+)", line)
+            if mt:
+                glob_time = float(mt.group(1))
+                if not want_residual:
+                    break
+            mr = re.match(r"residual: ([0-9.eE+-]+)", line)
+            if mr:
+                residual = float(mr.group(1))
+    finally:
+        rc = proc.poll()
+        if rc is None:
+            try:
+                os.killpg(proc.pid, signal.SIGTERM)  # exactly the process group we started
+            except ProcessLookupError:
+                pass
+            try:
+                proc.wait(timeout=10)
+            except subprocess.TimeoutExpired:
+                os.killpg(proc.pid, signal.SIGKILL)
+                proc.wait()
+    return {"glob_time": glob_time, "residual": residual, "rc": rc, "timed_out": timed_out,
+            "stdout": "".join(out_lines), "wall": time.time() - t0}
+
+
+def bench_line(n: int, m: int, ranks: int, steps: int, warmup: int, metric: str) -> dict:
+    err = ensure_built()
+    if err:
+        return {"impl": "reference", "unavailable": err}
+    budget = float(os.environ.get("JB_REF_BUDGET_S", "300"))
+    # calibrate on a small instance of the same m, then pick the largest n (halving from the
+    # headline size) whose predicted n^3 run time fits the budget
+    ncal = min(n, 2048)
+    cal = run_once(ncal, m, ranks, timeout_s=budget)
+    if cal["glob_time"] is None:
+        return {"impl": "reference", "unavailable": f"reference did not finish n={ncal} m={m} within {budget:.0f}s"}
+    # glob_time is printed with 2 decimals: use the wall clock when it is too coarse
+    tcal = cal["glob_time"] if cal["glob_time"] >= 0.5 else max(cal["glob_time"], 1e-3)
+    run_n = n
+    while run_n > ncal and tcal * (run_n / ncal) ** 3 > 0.8 * budget:
+        run_n //= 2
+    res = cal if run_n == ncal else run_once(run_n, m, ranks, timeout_s=budget)
+    if res["glob_time"] is None:
+        res, run_n = cal, ncal
+    sec = max(res["glob_time"], 5e-3)
+    out = {
+        "metric": metric, "value": 2.0 * run_n ** 3 / sec / 1e9, "unit": "GFLOP/s", "n_gpus": ranks,
+        "steps": 1, "warmup": 0, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "fp64", "data": "synthetic", "impl": "reference",
+        "config": {"model": "unmodified /root/reference/main.cpp (g++ -Ofast, MPI shim), generator |i-j|",
+                   "n": run_n, "m": m, "parallelism": f"{ranks} MPI ranks on the host CPUs (the reference has no GPU path)",
+                   "flop_convention": "2n^3 (the reference executes 3n^3)",
+                   "timer": "the program's own glob_time line (MPI_Wtime around Jordan, max over ranks)"},
+        "gpu_launches": 0,
+    }
+    if run_n != n:
+        out["config"]["note"] = (f"headline n={n} would take ~{tcal * (n / ncal) ** 3:.0f}s on this host "
+                                 f"(extrapolated from n={ncal}: {tcal:.2f}s, time ~ n^3); measured at the largest "
+                                 f"halved size that fits the {budget:.0f}s budget")
+        out["unavailable_at_headline_size"] = True
+    return out
+
+
+if __name__ == "__main__":
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 1200
+    m = int(sys.argv[2]) if len(sys.argv) > 2 else 60
+    p = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+    print(json.dumps(bench_line(n, m, p, 1, 0, "fp64_inverse_gflops")))

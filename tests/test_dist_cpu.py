@@ -1,0 +1,83 @@
+"""Multi-process CPU tests (gloo, world_size > 1) of the host-side distributed logic: block-cyclic
+scatter of a text file (C4), corner gather (C5), min-loc tie rules across ranks (C9), pivot-row
+broadcast (C10), cross-rank block-row swap (C11), error agreement (C3)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from mpi_jordan_crazy_acceleration_b200.models.eager import formula_rows
+from mpi_jordan_crazy_acceleration_b200.ops import cpu_block_jordan
+from mpi_jordan_crazy_acceleration_b200.utils import io as jio
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import json, os, sys
+sys.path.insert(0, %(root)r)
+import torch
+from mpi_jordan_crazy_acceleration_b200.parallel.comm import Comm
+from mpi_jordan_crazy_acceleration_b200.models.eager import EagerJordan
+from mpi_jordan_crazy_acceleration_b200.parallel.layout import Layout
+from mpi_jordan_crazy_acceleration_b200.utils import io as jio
+comm = Comm.init_from_env(prefer_cuda=False)
+out = []
+for fid, n, m in [(1, 100, 7), (6, 96, 12), (3, 24, 4), (1, 30, 8)]:
+    e = EagerJordan(n, m, comm=comm)
+    e.fill_formula(fid)
+    e.invert()
+    X = e.gather_inverse()
+    res = e.residual()
+    if comm.rank == 0:
+        out.append({"fid": fid, "n": n, "m": m, "piv": e.pivots, "X": X.tolist(), "res": res})
+path = sys.argv[1]
+lay = Layout(60, 8, comm.world, comm.rank)
+rows = jio.scatter_text_matrix(path, lay, comm)
+e = EagerJordan(60, 8, comm=comm)
+e.upload_local_rows(rows)
+e.invert()
+X = e.gather_inverse()
+c = jio.corner_from_rows(e.local_inverse(), lay, comm)
+err = None
+try:
+    jio.scatter_text_matrix(path + ".missing", lay, comm)
+except jio.MatrixFileError as exc:
+    err = exc.code
+codes = comm.allgather_obj(err)
+if comm.rank == 0:
+    out.append({"file": True, "X": X.tolist(), "corner": c.tolist(), "piv": e.pivots, "codes": codes})
+    print("RESULT " + json.dumps(out))
+'''
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_eager_gloo_world(world, tmp_path):
+    torch.manual_seed(11)
+    A = torch.randn(60, 60, dtype=torch.float64)
+    path = tmp_path / "m.txt"
+    jio.write_matrix(str(path), A)
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % {"root": ROOT})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + world), str(script), str(path)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT ")]
+    assert line, r.stdout[-2000:] + r.stderr[-2000:]
+    import json
+
+    res = json.loads(line[-1][7:])
+    for rec in res[:-1]:
+        A_f = formula_rows(rec["fid"], rec["n"], torch.arange(rec["n"]))
+        Xo, piv = cpu_block_jordan(A_f, rec["m"], world)      # oracle emulating `world` ranks
+        assert rec["piv"] == piv
+        assert torch.allclose(torch.tensor(rec["X"], dtype=torch.float64), Xo, atol=1e-9)
+        assert rec["res"] < 1e-8
+    f = res[-1]
+    Xo, piv = cpu_block_jordan(A, 8, world)
+    assert f["piv"] == piv
+    assert torch.allclose(torch.tensor(f["X"], dtype=torch.float64), Xo, atol=1e-9)
+    assert torch.allclose(torch.tensor(f["corner"], dtype=torch.float64), Xo[:10, :10], atol=1e-9)
+    assert f["codes"] == [-1] * world          # every rank agreed on "cannot open"
