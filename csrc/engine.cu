@@ -74,7 +74,12 @@ struct JbEngine {
   int64_t n, Nr, ldw, rows_loc;
   int m, p, rank, Kp, rloc, nsub, CT, sm_count;
   // local buffers
-  double *W = nullptr, *Lbuf = nullptr, *invbuf = nullptr, *normbuf = nullptr, *Acopy = nullptr;
+  double *W = nullptr, *invbuf = nullptr, *normbuf = nullptr, *Acopy = nullptr;
+  double* Lbuf[2] = {nullptr, nullptr};  // L panel of step t lives in Lbuf[t & 1] (look-ahead)
+  uint32_t* counters = nullptr;          // one work-item counter per step-kernel launch
+  cudaStream_t hstream = nullptr;        // high-priority stream running K1(t+1) beside step_B(t)
+  cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr};
+  bool lookahead = true;
   int* okbuf = nullptr;
   JbCtl* ctl = nullptr;
   JbStepInfo* stepinfo = nullptr;
@@ -107,7 +112,7 @@ int build_maps(JbEngine* e) {
     if ((rc = make_map(&M.tmW, e->W, e->ldw, e->rows_loc, e->ldw, JB_RS, JB_BK))) return rc;
     if ((rc = make_map(&M.tmRow, loc + e->off_rowbuf[par], e->ldw, e->Kp, e->ldw, JB_RS, JB_BK)))
       return rc;
-    if ((rc = make_map(&M.tmL, e->Lbuf, e->Kp, e->rows_loc, e->Kp, JB_LS, JB_BM))) return rc;
+    if ((rc = make_map(&M.tmL, e->Lbuf[par], e->Kp, e->rows_loc, e->Kp, JB_LS, JB_BM))) return rc;
     if ((rc = make_map(&M.tmInv, e->invbuf, e->Kp, (uint64_t)e->rloc * e->Kp, e->Kp, JB_LS, JB_BM)))
       return rc;
     if ((rc = make_map(&M.tmSwap, loc + e->off_swapbuf, e->ldw, e->Kp, e->ldw, JB_LS, JB_BM)))
@@ -157,7 +162,9 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   const size_t rl = (size_t)std::max<int64_t>(e->rows_loc, 1);
   cudaError_t r = cudaSuccess;
   if (r == cudaSuccess) r = dmalloc((void**)&e->W, rl * e->ldw * 8);
-  if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf, (rl + JB_BM) * e->Kp * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[0], (rl + JB_BM) * e->Kp * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[1], (rl + JB_BM) * e->Kp * 8);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(2 * e->Nr + 2) * 4);
   if (r == cudaSuccess)
     r = dmalloc((void**)&e->invbuf, ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->normbuf, (size_t)std::max(e->rloc, 1) * 8);
@@ -186,6 +193,17 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   e->symm_bytes = align_up(off, 4096);
   e->W_peers[e->rank] = e->W;
   if (getenv("JB_TIME_KERNELS")) e->profile = true;
+  if (getenv("JB_NO_LOOKAHEAD")) e->lookahead = false;
+  {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (cudaStreamCreateWithPriority(&e->hstream, cudaStreamNonBlocking, hi) != cudaSuccess) e->lookahead = false;
+    for (int i = 0; i < 2 && e->lookahead; ++i) {
+      if (cudaEventCreateWithFlags(&e->evA[i], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&e->evK[i], cudaEventDisableTiming) != cudaSuccess)
+        e->lookahead = false;
+    }
+  }
   *out = e;
   return JB_OK;
 }
@@ -202,7 +220,13 @@ void jb_engine_destroy(JbEngine* e) {
           if (ptr) cudaIpcCloseMemHandle(ptr);
         }
   if (e->own_symm && e->symm_peers[e->rank]) cudaFree(e->symm_peers[e->rank]);
-  cudaFree(e->W); cudaFree(e->Lbuf); cudaFree(e->invbuf); cudaFree(e->normbuf); cudaFree(e->okbuf);
+  if (e->hstream) cudaStreamDestroy(e->hstream);
+  for (int i = 0; i < 2; ++i) {
+    if (e->evA[i]) cudaEventDestroy(e->evA[i]);
+    if (e->evK[i]) cudaEventDestroy(e->evK[i]);
+  }
+  cudaFree(e->counters);
+  cudaFree(e->W); cudaFree(e->Lbuf[0]); cudaFree(e->Lbuf[1]); cudaFree(e->invbuf); cudaFree(e->normbuf); cudaFree(e->okbuf);
   cudaFree(e->ctl); cudaFree(e->stepinfo); cudaFree(e->rowsum); cudaFree(e->scratch_max);
   cudaFree(e->Acopy); cudaFree(e->Xp); cudaFree(e->Rslab);
   delete e;
@@ -374,8 +398,9 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   JB_CHECK(cudaMemsetAsync(e->ctl, 0, offsetof(JbCtl, norm_a), st));
 
+  JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(2 * e->Nr + 2) * 4, st));
   K1Params K;
-  K.W = e->W; K.Lbuf = e->Lbuf; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
+  K.W = e->W; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
   K.ctl = e->ctl; K.stepinfo = e->stepinfo;
   for (int r = 0; r < JB_MAX_RANKS; ++r)
     K.mail_peers[r] = r < e->p ? (JbMail*)(e->symm_peers[r] + e->off_mail) : nullptr;
@@ -391,26 +416,31 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   }
   const int grid = 2 * e->sm_count;
   const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
-
   if (e->profile && e->ev.size() < (size_t)(2 * e->Nr + 2)) {
     size_t old = e->ev.size();
     e->ev.resize((size_t)(2 * e->Nr + 2));
     for (size_t i = old; i < e->ev.size(); ++i) JB_CHECK(cudaEventCreate(&e->ev[i]));
   }
-  for (int64_t t = 0; t < e->Nr; ++t) {
-    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t], st));
-    const uint32_t g = e->gstep++;
-    const int par = g & 1;
-    // ---- K1: candidates are local block rows with global index >= t (main.cpp:1028)
-    int64_t s0 = t > e->rank ? (t - e->rank + e->p - 1) / e->p : 0;
+  const uint32_t g0 = e->gstep;
+  e->gstep += (uint32_t)e->Nr;
+  const bool la = e->lookahead && e->Nr > 1;
+
+  // K1 of step t: candidates are the local block rows with global index >= t (main.cpp:1028)
+  auto launch_k1 = [&](int64_t t, cudaStream_t s) -> cudaError_t {
+    const uint32_t g = g0 + (uint32_t)t;
+    const int64_t s0 = t > e->rank ? (t - e->rank + e->p - 1) / e->p : 0;
     K.t = (int)t;
     K.s0 = (int)s0;
     K.ncand = (int)std::max<int64_t>(0, e->rloc - s0);
     K.ngroups = std::max(K.ncand, 1);
     K.tag = g + 1;
-    JB_CHECK(jb_launch_k1(K, panel_ctas, st));
-    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t + 1], st));
-    // ---- fused scale + broadcast + swap + trailing update
+    K.Lbuf = e->Lbuf[g & 1];
+    e->launches += 1;
+    return jb_launch_k1(K, panel_ctas, s);
+  };
+  auto launch_step = [&](int64_t t, int phase, cudaStream_t s) -> cudaError_t {
+    const uint32_t g = g0 + (uint32_t)t;
+    const int par = g & 1;
     S.t = (int)t;
     S.t_slot = (t % e->p == e->rank) ? (int)(t / e->p) : -1;
     S.row_expect = ((g >> 1) + 1) * (uint32_t)e->nsub;
@@ -421,8 +451,34 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     }
     S.rowbuf_mc = e->symm_mc ? (double*)(e->symm_mc + e->off_rowbuf[par]) : nullptr;
     S.rowflag_mc = e->symm_mc ? (uint32_t*)(e->symm_mc + e->off_rowflag[par]) : nullptr;
-    JB_CHECK(jb_launch_step(S, e->maps[par], grid, st));
-    e->launches += 2;
+    S.phase = phase;
+    // priority column tiles = the ones covering block column t+1 (what K1(t+1) reads)
+    S.pct0 = (int)(((t + 1) * e->m) / JB_BN);
+    S.pct1 = (int)std::min<int64_t>(e->CT - 1, ((t + 2) * e->m - 1) / JB_BN);
+    S.counter = e->counters + 2 * t + (phase == JB_PHASE_B ? 1 : 0);
+    e->launches += 1;
+    return jb_launch_step(S, e->maps[par], grid, s);
+  };
+
+  JB_CHECK(launch_k1(0, st));
+  for (int64_t t = 0; t < e->Nr; ++t) {
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t], st));
+    if (la && t + 1 < e->Nr) {
+      // step_A(t): scale + broadcast, row swap, and the update of block column t+1
+      JB_CHECK(launch_step(t, JB_PHASE_A, st));
+      JB_CHECK(cudaEventRecord(e->evA[t & 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t + 1], st));
+      // K1(t+1) on the high-priority stream, enqueued BEFORE step_B(t) so its CTAs get SMs first
+      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evA[t & 1], 0));
+      JB_CHECK(launch_k1(t + 1, e->hstream));
+      JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
+      JB_CHECK(launch_step(t, JB_PHASE_B, st));
+      JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
+    } else {
+      JB_CHECK(launch_step(t, JB_PHASE_ALL, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t + 1], st));
+      if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
+    }
   }
   if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * e->Nr], st));
   JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
@@ -435,8 +491,8 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       float a = 0, b = 0;
       JB_CHECK(cudaEventElapsedTime(&a, e->ev[2 * t], e->ev[2 * t + 1]));
       JB_CHECK(cudaEventElapsedTime(&b, e->ev[2 * t + 1], e->ev[2 * t + 2]));
-      e->prof_k1_ms += a;
-      e->prof_step_ms += b;
+      e->prof_k1_ms += a;   // look-ahead: step_A(t); else: the fused step kernel
+      e->prof_step_ms += b; // look-ahead: step_B(t) (+ wait for K1(t+1)); else: K1(t+1)
     }
     float c = 0;
     JB_CHECK(cudaEventElapsedTime(&c, e->ev[2 * e->Nr], e->ev[2 * e->Nr + 1]));

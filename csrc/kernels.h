@@ -44,7 +44,11 @@ struct StepParams {
   int t_slot;             // local slot of block row t on its owner, else -1
   uint32_t row_expect;    // rowflag value meaning "tile landed"
   uint32_t tag;           // swapflag value for this step
+  int phase;              // JB_PHASE_ALL / _A / _B (look-ahead split)
+  int pct0, pct1;         // priority column tiles (cover block column t+1); empty if pct1 < pct0
+  uint32_t* counter;      // work-item counter of THIS launch (zeroed by the host)
 };
+enum { JB_PHASE_ALL = 0, JB_PHASE_A = 1, JB_PHASE_B = 2 };
 struct StepMaps {
   CUtensorMap tmW;     // W              box {JB_RS, JB_BK}
   CUtensorMap tmRow;   // rowbuf[par]    box {JB_RS, JB_BK}

@@ -29,6 +29,7 @@ constexpr int STEP_THREADS = (MMA_WARPS + 1) * 32;  // + 1 TMA producer warp
 constexpr int L_BYTES = JB_LS * JB_BM * 8;          // 10240
 constexpr int R_BYTES = JB_RS * JB_BK * 8;          // 16896
 constexpr int STAGE_BYTES = L_BYTES + R_BYTES;      // 27136
+constexpr int RING = 4;                             // depth of the claimed-item ring
 
 enum { IT_SCALE = 0, IT_ROWT = 1, IT_UPD = 2, IT_UPD_SWAPPED = 3 };
 
@@ -42,17 +43,37 @@ struct Item {
 
 struct Plan {
   int nscale, nrowt, nupd, total;
-  int rtu;  // row tiles taking part in UPD
+  int rtu;   // row tiles taking part in UPD
+  int npri;  // priority column tiles (they cover block column t+1, needed first by K1(t+1))
 };
 
+// Work list per phase (items are claimed IN ORDER from a global counter, so anything an item waits
+// for inside the same launch has a lower index and is already running):
+//   ALL : SCALE, ROWT, UPD over every column tile              (no look-ahead)
+//   A   : SCALE (priority column tiles first), ROWT, UPD of the priority column tiles
+//   B   : UPD of all other column tiles  (overlaps with K1(t+1) running on another stream)
 __device__ __forceinline__ Plan make_plan(const StepParams& P, const JbStepInfo& si) {
   Plan pl;
-  pl.nscale = (si.piv_rank == P.rank) ? P.nsub * P.CT : 0;
-  pl.nrowt = (P.t_slot >= 0) ? P.CT : 0;
+  pl.npri = (P.phase == JB_PHASE_ALL || P.pct1 < P.pct0) ? 0 : (P.pct1 - P.pct0 + 1);
   pl.rtu = (P.rloc - (P.t_slot >= 0 ? 1 : 0)) * P.nsub;
-  pl.nupd = pl.rtu * P.CT;
+  if (P.phase == JB_PHASE_B) {
+    pl.nscale = 0;
+    pl.nrowt = 0;
+    pl.nupd = pl.rtu * (P.CT - pl.npri);
+  } else {
+    pl.nscale = (si.piv_rank == P.rank) ? P.nsub * P.CT : 0;
+    pl.nrowt = (P.t_slot >= 0) ? P.CT : 0;
+    pl.nupd = pl.rtu * (P.phase == JB_PHASE_ALL ? P.CT : pl.npri);
+  }
   pl.total = pl.nscale + pl.nrowt + pl.nupd;
   return pl;
+}
+
+// position in "priority tiles first" order -> column tile
+__device__ __forceinline__ int ct_priority_first(const StepParams& P, const Plan& pl, int pos) {
+  if (pos < pl.npri) return P.pct0 + pos;
+  const int c = pos - pl.npri;
+  return c < P.pct0 ? c : c + pl.npri;
 }
 
 __device__ __forceinline__ Item decode(const StepParams& P, const JbStepInfo& si, const Plan& pl,
@@ -60,18 +81,22 @@ __device__ __forceinline__ Item decode(const StepParams& P, const JbStepInfo& si
   Item it;
   if (idx < pl.nscale) {
     it.type = IT_SCALE;
-    it.ct = idx / P.nsub;
-    it.sub = idx - it.ct * P.nsub;
+    const int pos = idx / P.nsub;
+    it.sub = idx - pos * P.nsub;
+    it.ct = ct_priority_first(P, pl, pos);
     it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
   } else if (idx < pl.nscale + pl.nrowt) {
     it.type = IT_ROWT;
-    it.ct = idx - pl.nscale;
+    it.ct = ct_priority_first(P, pl, idx - pl.nscale);
     it.sub = 0;
     it.lrow0 = P.t_slot * P.m;
   } else {
     int u = idx - pl.nscale - pl.nrowt;
-    it.ct = u / pl.rtu;
-    int rt = u - it.ct * pl.rtu;
+    const int cpos = u / pl.rtu;
+    int rt = u - cpos * pl.rtu;
+    if (P.phase == JB_PHASE_A) it.ct = P.pct0 + cpos;
+    else if (P.phase == JB_PHASE_B) it.ct = cpos < P.pct0 ? cpos : cpos + pl.npri;
+    else it.ct = cpos;
     int slot = rt / P.nsub;
     it.sub = rt - slot * P.nsub;
     if (P.t_slot >= 0 && slot >= P.t_slot) slot += 1;  // skip block row t (handled by ROWT)
@@ -94,6 +119,12 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t full_bar[JB_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[JB_STAGES];
+  // work ring: the producer thread claims items from the global counter and hands them to the MMA
+  // warps (dynamic scheduling: a CTA that starts late, e.g. after a K1 CTA left its SM, simply
+  // takes whatever work is left)
+  __shared__ __align__(8) uint64_t ring_full[RING];
+  __shared__ __align__(8) uint64_t ring_empty[RING];
+  __shared__ int ring_item[RING];
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -102,7 +133,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   if (P.ctl->singular) return;
   const JbStepInfo si = P.stepinfo[P.t];
   const Plan pl = make_plan(P, si);
-  if ((int)blockIdx.x >= pl.total) return;
+  if (pl.total == 0) return;
 
 #ifdef JB_DBG_GENERIC
   unsigned char* stage_base =
@@ -115,6 +146,10 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
     for (int s = 0; s < JB_STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], MMA_WARPS);
+    }
+    for (int s = 0; s < RING; ++s) {
+      mbar_init(&ring_full[s], 1);
+      mbar_init(&ring_empty[s], MMA_WARPS);
     }
     mbar_fence_init();
   }
@@ -138,7 +173,13 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
       tma_prefetch_desc(&M.tmInv);
       tma_prefetch_desc(&M.tmSwap);
       uint32_t it_cnt = 0;
-      for (int idx = blockIdx.x; idx < pl.total; idx += gridDim.x) {
+      for (uint32_t rp = 0;; ++rp) {
+        const int idx = (int)atomicAdd(P.counter, 1u);
+        const int slot = rp % RING;
+        mbar_wait(&ring_empty[slot], ((rp / RING) & 1) ^ 1);
+        ring_item[slot] = idx;
+        mbar_arrive(&ring_full[slot]);  // release: publishes ring_item[slot]
+        if (idx >= pl.total) break;
         const Item it = decode(P, si, pl, idx);
         if (it.type == IT_ROWT) continue;
         const int col0 = it.ct * JB_BN;
@@ -176,7 +217,13 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   const int wn = warp;  // 4 warps side by side along N, each 64 x 32
   uint32_t it_cnt = 0;
 
-  for (int idx = blockIdx.x; idx < pl.total; idx += gridDim.x) {
+  for (uint32_t rc = 0;; ++rc) {
+    const int rslot = rc % RING;
+    mbar_wait(&ring_full[rslot], (rc / RING) & 1);
+    const int idx = ring_item[rslot];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&ring_empty[rslot]);
+    if (idx >= pl.total) break;
     const Item it = decode(P, si, pl, idx);
     const int col0 = it.ct * JB_BN;
 

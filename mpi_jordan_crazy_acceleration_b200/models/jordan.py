@@ -266,7 +266,12 @@ class JordanSolver:
         step kernels, and the final un-permutation.  Needs ``set_profiling(True)``."""
         a, b, c = C.c_double(), C.c_double(), C.c_double()
         _native.check(self.lib.jb_engine_phase_times(self._h, C.byref(a), C.byref(b), C.byref(c)))
-        return {"k1_ms": a.value, "step_ms": b.value, "tail_ms": c.value}
+        if os.environ.get("JB_NO_LOOKAHEAD"):
+            # serial schedule: fused step kernel of step t, then K1(t+1)
+            return {"step_ms": a.value, "k1_ms": b.value, "tail_ms": c.value, "lookahead": False}
+        # look-ahead: step_A(t) (scale/broadcast/swap + block column t+1), then step_B(t) with
+        # K1(t+1) running beside it on the high-priority stream
+        return {"stepA_ms": a.value, "stepB_ms": b.value, "tail_ms": c.value, "lookahead": True}
 
     @property
     def launch_count(self) -> int:

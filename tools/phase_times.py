@@ -20,10 +20,9 @@ def main():
             sec = s.invert()
         pt = s.phase_times()
         tf = 2.0 * n ** 3 / sec / 1e12
-        step_tf = 2.0 * n ** 3 / (pt["step_ms"] * 1e-3) / 1e12
-        print(json.dumps({"n": n, "m": m, "seconds": sec, "tflops": tf, "step_only_tflops": step_tf,
-                          "k1_us_per_step": pt["k1_ms"] * 1e3 / s.layout.Nr,
-                          "step_us_per_step": pt["step_ms"] * 1e3 / s.layout.Nr, **pt}), flush=True)
+        Nr = s.layout.Nr
+        per = {k.replace("_ms", "_us_per_step"): v * 1e3 / Nr for k, v in pt.items() if k.endswith("_ms")}
+        print(json.dumps({"n": n, "m": m, "seconds": sec, "tflops": tf, **per, **pt}), flush=True)
         s.close()
         torch.cuda.synchronize()
 
