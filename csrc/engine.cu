@@ -99,7 +99,7 @@ struct JbEngine {
   // optional per-kernel timing (JB_TIME_KERNELS=1 or jb_engine_set_profiling)
   bool profile = false;
   std::vector<cudaEvent_t> ev;
-  double prof_k1_ms = 0, prof_step_ms = 0, prof_tail_ms = 0;
+  double prof_k1_ms = 0, prof_step_ms = 0, prof_tail_ms = 0, prof_wait_ms = 0;
 };
 
 namespace {
@@ -188,7 +188,7 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   const size_t fb = align_up((size_t)e->CT * 4, 256);
   e->off_rowflag[0] = off; off += fb;
   e->off_rowflag[1] = off; off += fb;
-  e->off_swapflag = off; off += fb;
+  e->off_swapflag = off; off += align_up((size_t)e->CT * e->nsub * 4, 256);  // one flag per 64-row chunk
   e->off_mail = off; off += align_up(2 * JB_MAX_RANKS * sizeof(JbMail), 256);
   e->symm_bytes = align_up(off, 4096);
   e->W_peers[e->rank] = e->W;
@@ -416,9 +416,9 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   }
   const int grid = 2 * e->sm_count;
   const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
-  if (e->profile && e->ev.size() < (size_t)(2 * e->Nr + 2)) {
+  if (e->profile && e->ev.size() < (size_t)(3 * e->Nr + 2)) {
     size_t old = e->ev.size();
-    e->ev.resize((size_t)(2 * e->Nr + 2));
+    e->ev.resize((size_t)(3 * e->Nr + 2));
     for (size_t i = old; i < e->ev.size(); ++i) JB_CHECK(cudaEventCreate(&e->ev[i]));
   }
   const uint32_t g0 = e->gstep;
@@ -462,40 +462,44 @@ int jb_engine_invert(JbEngine* e, void* stream) {
 
   JB_CHECK(launch_k1(0, st));
   for (int64_t t = 0; t < e->Nr; ++t) {
-    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t], st));
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t], st));
     if (la && t + 1 < e->Nr) {
       // step_A(t): scale + broadcast, row swap, and the update of block column t+1
       JB_CHECK(launch_step(t, JB_PHASE_A, st));
       JB_CHECK(cudaEventRecord(e->evA[t & 1], st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));
       // K1(t+1) on the high-priority stream, enqueued BEFORE step_B(t) so its CTAs get SMs first
       JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evA[t & 1], 0));
       JB_CHECK(launch_k1(t + 1, e->hstream));
       JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
       JB_CHECK(launch_step(t, JB_PHASE_B, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
       JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
     } else {
       JB_CHECK(launch_step(t, JB_PHASE_ALL, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
     }
   }
-  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2 * e->Nr], st));
+  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * e->Nr], st));
   JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
   e->launches += (e->rows_loc > 0);
   if (e->profile) {
-    JB_CHECK(cudaEventRecord(e->ev[2 * e->Nr + 1], st));
+    JB_CHECK(cudaEventRecord(e->ev[3 * e->Nr + 1], st));
     JB_CHECK(cudaStreamSynchronize(st));
-    e->prof_k1_ms = e->prof_step_ms = 0;
+    e->prof_k1_ms = e->prof_step_ms = e->prof_wait_ms = 0;
     for (int64_t t = 0; t < e->Nr; ++t) {
-      float a = 0, b = 0;
-      JB_CHECK(cudaEventElapsedTime(&a, e->ev[2 * t], e->ev[2 * t + 1]));
-      JB_CHECK(cudaEventElapsedTime(&b, e->ev[2 * t + 1], e->ev[2 * t + 2]));
-      e->prof_k1_ms += a;   // look-ahead: step_A(t); else: the fused step kernel
-      e->prof_step_ms += b; // look-ahead: step_B(t) (+ wait for K1(t+1)); else: K1(t+1)
+      float a = 0, b = 0, c = 0;
+      JB_CHECK(cudaEventElapsedTime(&a, e->ev[3 * t], e->ev[3 * t + 1]));
+      JB_CHECK(cudaEventElapsedTime(&b, e->ev[3 * t + 1], e->ev[3 * t + 2]));
+      JB_CHECK(cudaEventElapsedTime(&c, e->ev[3 * t + 2], e->ev[3 * t + 3]));
+      e->prof_k1_ms += a;    // look-ahead: step_A(t); serial: the fused step kernel
+      e->prof_step_ms += b;  // look-ahead: step_B(t); serial: K1(t+1)
+      e->prof_wait_ms += c;  // look-ahead: time the main stream then still waits for K1(t+1)
     }
     float c = 0;
-    JB_CHECK(cudaEventElapsedTime(&c, e->ev[2 * e->Nr], e->ev[2 * e->Nr + 1]));
+    JB_CHECK(cudaEventElapsedTime(&c, e->ev[3 * e->Nr], e->ev[3 * e->Nr + 1]));
     e->prof_tail_ms = c;
   }
   return JB_OK;
@@ -512,6 +516,8 @@ int jb_engine_phase_times(JbEngine* e, double* k1_ms, double* step_ms, double* t
   *tail_ms = e->prof_tail_ms;
   return JB_OK;
 }
+
+double jb_engine_wait_ms(JbEngine* e) { return e->prof_wait_ms; }
 
 int jb_engine_status(JbEngine* e, void* stream) {
   JB_CHECK(cudaSetDevice(e->cfg.device));

@@ -62,7 +62,7 @@ __device__ __forceinline__ Plan make_plan(const StepParams& P, const JbStepInfo&
     pl.nupd = pl.rtu * (P.CT - pl.npri);
   } else {
     pl.nscale = (si.piv_rank == P.rank) ? P.nsub * P.CT : 0;
-    pl.nrowt = (P.t_slot >= 0) ? P.CT : 0;
+    pl.nrowt = (P.t_slot >= 0) ? P.CT * P.nsub : 0;
     pl.nupd = pl.rtu * (P.phase == JB_PHASE_ALL ? P.CT : pl.npri);
   }
   pl.total = pl.nscale + pl.nrowt + pl.nupd;
@@ -87,9 +87,10 @@ __device__ __forceinline__ Item decode(const StepParams& P, const JbStepInfo& si
     it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
   } else if (idx < pl.nscale + pl.nrowt) {
     it.type = IT_ROWT;
-    it.ct = ct_priority_first(P, pl, idx - pl.nscale);
-    it.sub = 0;
-    it.lrow0 = P.t_slot * P.m;
+    const int pos = (idx - pl.nscale) / P.nsub;
+    it.sub = (idx - pl.nscale) - pos * P.nsub;
+    it.ct = ct_priority_first(P, pl, pos);
+    it.lrow0 = P.t_slot * P.m + it.sub * JB_BM;
   } else {
     int u = idx - pl.nscale - pl.nrowt;
     const int cpos = u / pl.rtu;
@@ -114,6 +115,9 @@ __device__ __forceinline__ void st_f64x2(double* p, double x, double y) {
   *reinterpret_cast<double2*>(p) = make_double2(x, y);
 }
 
+// kUpdOnly = true is the phase-B specialisation: only UPD items exist, so the SCALE / ROWT code is
+// compiled out and cannot disturb the register allocation of the DMMA loop.
+template <bool kUpdOnly>
 __global__ void __launch_bounds__(STEP_THREADS, 2)
 k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -181,12 +185,12 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         mbar_arrive(&ring_full[slot]);  // release: publishes ring_item[slot]
         if (idx >= pl.total) break;
         const Item it = decode(P, si, pl, idx);
-        if (it.type == IT_ROWT) continue;
+        if (!kUpdOnly && it.type == IT_ROWT) continue;
         const int col0 = it.ct * JB_BN;
-        if (it.type != IT_SCALE) {
+        if (kUpdOnly || it.type != IT_SCALE) {
           wait_flag_ge(rowflag_local + it.ct, P.row_expect);  // pivot-row tile landed
           if (it.type == IT_UPD_SWAPPED)
-            for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c, P.tag);
+            for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c * P.nsub + it.sub, P.tag);
           fence_proxy_async();  // remote generic-proxy writes -> my async-proxy (TMA) reads
         }
         for (int c = 0; c < KC; ++c, ++it_cnt) {
@@ -196,7 +200,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           unsigned char* sb = stage_base + (size_t)s * STAGE_BYTES;
           mbar_expect_tx(&full_bar[s], STAGE_BYTES);
           const int k0 = c * JB_BK;
-          if (it.type == IT_SCALE) {
+          if (!kUpdOnly && it.type == IT_SCALE) {
             tma_load_2d(sb, &M.tmInv, k0, si.piv_slot * P.Kp + it.sub * JB_BM, &full_bar[s]);
             tma_load_2d(sb + L_BYTES, &M.tmW, col0, si.piv_slot * P.m + k0, &full_bar[s]);
           } else if (it.type == IT_UPD) {
@@ -227,37 +231,51 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
     const Item it = decode(P, si, pl, idx);
     const int col0 = it.ct * JB_BN;
 
-    if (it.type == IT_ROWT) {
-      // ---- K4: swap + install the scaled pivot row as block row t
+    if (!kUpdOnly && it.type == IT_ROWT) {
+      // ---- K4: swap + install the scaled pivot row as block row t (one 64-row chunk per item).
+      //      Thread -> (column pair v, row parity); 4 independent 16-byte loads in flight per thread.
       const int ncol = (int)min((int64_t)JB_BN, P.ldw - col0);  // multiple of 16
       const int vec_per_row = ncol / 2;
-      double* wrow = P.W + (int64_t)it.lrow0 * P.ldw + col0;
+      const int v = tid & 63, rh = tid >> 6;
+      const bool vok = v < vec_per_row;
+      const int64_t roff = (int64_t)(it.sub * JB_BM) * P.ldw + col0 + 2 * v;
+      double* wrow = P.W + (int64_t)P.t_slot * P.m * P.ldw + roff;
       if (si.do_swap) {
-        double* dst = P.swapbuf_peers[si.piv_rank] + col0;
-        for (int e = tid; e < P.m * vec_per_row; e += MMA_WARPS * 32) {
-          int r = e / vec_per_row, v = e - r * vec_per_row;
-          double2 x = ld_f64x2(wrow + (int64_t)r * P.ldw + 2 * v);
-          st_f64x2(dst + (int64_t)r * P.ldw + 2 * v, x.x, x.y);
+        double* dst = P.swapbuf_peers[si.piv_rank] + roff;
+        for (int r0 = rh; r0 < it.rows_valid; r0 += 8) {
+          double2 x[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (vok && r0 + 2 * u < it.rows_valid) x[u] = ld_f64x2(wrow + (int64_t)(r0 + 2 * u) * P.ldw);
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (vok && r0 + 2 * u < it.rows_valid)
+              st_f64x2(dst + (int64_t)(r0 + 2 * u) * P.ldw, x[u].x, x[u].y);
         }
         __threadfence_system();
         named_bar_sync(1, MMA_WARPS * 32);
-        if (tid == 0) st_release_sys_u32(P.swapflag_peers[si.piv_rank] + it.ct, P.tag);
+        if (tid == 0) st_release_sys_u32(P.swapflag_peers[si.piv_rank] + it.ct * P.nsub + it.sub, P.tag);
       }
       if (lane == 0) wait_flag_ge(rowflag_local + it.ct, P.row_expect);
       __syncwarp();
-      const double* src = rowbuf_local + col0;
-      for (int e = tid; e < P.m * vec_per_row; e += MMA_WARPS * 32) {
-        int r = e / vec_per_row, v = e - r * vec_per_row;
-        double2 x = ld_f64x2(src + (int64_t)r * P.ldw + 2 * v);
-        st_f64x2(wrow + (int64_t)r * P.ldw + 2 * v, -x.x, -x.y);  // rowbuf holds -R
+      const double* src = rowbuf_local + roff;
+      for (int r0 = rh; r0 < it.rows_valid; r0 += 8) {
+        double2 x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (vok && r0 + 2 * u < it.rows_valid) x[u] = ld_f64x2(src + (int64_t)(r0 + 2 * u) * P.ldw);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (vok && r0 + 2 * u < it.rows_valid)
+            st_f64x2(wrow + (int64_t)(r0 + 2 * u) * P.ldw, -x[u].x, -x[u].y);  // rowbuf holds -R
       }
       continue;
     }
 
     // ---- accumulator init
     double acc[8][4][2];
-    const bool upd = (it.type != IT_SCALE);
-    if (it.type == IT_SCALE) {
+    const bool upd = kUpdOnly || (it.type != IT_SCALE);
+    if (!kUpdOnly && it.type == IT_SCALE) {
 #pragma unroll
       for (int mt = 0; mt < 8; ++mt)
 #pragma unroll
@@ -268,7 +286,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         cbase = P.W + (int64_t)it.lrow0 * P.ldw;
       } else {
         if (lane == 0) {
-          wait_flag_ge(swapflag_local + it.ct, P.tag);
+          wait_flag_ge(swapflag_local + it.ct * P.nsub + it.sub, P.tag);
         }
         __syncwarp();
         cbase = swapbuf_local + (int64_t)(it.sub * JB_BM) * P.ldw;
@@ -384,11 +402,17 @@ cudaError_t jb_launch_step(const StepParams& P, const StepMaps& M, int grid, cud
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev % JB_MAX_RANKS]) {
-    cudaError_t e = cudaFuncSetAttribute(k_step_fused, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(k_step_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)jb_step_smem_bytes());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_step_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)jb_step_smem_bytes());
     if (e != cudaSuccess) return e;
     configured[dev % JB_MAX_RANKS] = true;
   }
-  k_step_fused<<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
+  if (P.phase == JB_PHASE_B)
+    k_step_fused<true><<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
+  else
+    k_step_fused<false><<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
   return cudaGetLastError();
 }

@@ -105,6 +105,7 @@ int64_t jb_engine_launch_count(const JbEngine* e); /* kernels launched by this e
 /* per-kernel CUDA-event timing of the last jb_engine_invert (adds a stream sync; off by default) */
 int jb_engine_set_profiling(JbEngine* e, int on);
 int jb_engine_phase_times(JbEngine* e, double* k1_ms, double* step_ms, double* tail_ms);
+double jb_engine_wait_ms(JbEngine* e); /* look-ahead: time the main stream still waited for K1(t+1) */
 
 /* results */
 void* jb_engine_w_ptr(JbEngine* e);

@@ -97,6 +97,7 @@ def _declare_cuda(lib) -> None:
         "jb_engine_launch_count": (i64, [vp]),
         "jb_engine_set_profiling": (C.c_int, [vp, C.c_int]),
         "jb_engine_phase_times": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+        "jb_engine_wait_ms": (C.c_double, [vp]),
         "jb_engine_w_ptr": (vp, [vp]),
         "jb_engine_ldw": (i64, [vp]),
         "jb_engine_local_rows": (i64, [vp]),

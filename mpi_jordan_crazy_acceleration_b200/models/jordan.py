@@ -271,7 +271,8 @@ class JordanSolver:
             return {"step_ms": a.value, "k1_ms": b.value, "tail_ms": c.value, "lookahead": False}
         # look-ahead: step_A(t) (scale/broadcast/swap + block column t+1), then step_B(t) with
         # K1(t+1) running beside it on the high-priority stream
-        return {"stepA_ms": a.value, "stepB_ms": b.value, "tail_ms": c.value, "lookahead": True}
+        return {"stepA_ms": a.value, "stepB_ms": b.value, "k1_wait_ms": float(self.lib.jb_engine_wait_ms(self._h)),
+                "tail_ms": c.value, "lookahead": True}
 
     @property
     def launch_count(self) -> int:
