@@ -107,4 +107,30 @@ cudaError_t jb_launch_gather_panel(const GatherParams& P, cudaStream_t st);
 cudaError_t jb_launch_dist_gemm(const DistGemmParams& P, cudaStream_t st);
 cudaError_t jb_launch_max_reduce(const double* v, int64_t count, double* out, cudaStream_t st);
 
+// ------------------------------------------------------------------ K3b tcgen05 int8-split update
+struct Tc05Launch {
+  double* C;
+  int64_t ldc, rows, cols;
+  const int8_t* Lq;       // [S][KB][rows_pad][128]
+  const int8_t* Rq;       // [S][KB][cols_pad][128]
+  int64_t rows_pad, cols_pad;
+  const double* rscale;   // [rows]
+  const double* cscale;   // [cols_pad]
+  int K, S, grid;
+  int64_t skip0, skiplen; // local rows handled elsewhere (block row t)
+  const JbCtl* ctl;
+  const JbStepInfo* stepinfo;
+  int t, m, rank;
+  int col_t0, col_t1;     // column slot t (accumulate from zero), -1/-1 = none
+};
+size_t jb_tc05_smem_bytes(int S);
+size_t jb_tc05_lq_bytes(int64_t rows_pad, int K, int S);
+size_t jb_tc05_rq_bytes(int64_t cols_pad, int K, int S);
+cudaError_t jb_tc05_slice_rows(const double* L, int64_t ldl, int64_t rows, int K, int S, int8_t* Lq,
+                               int64_t rows_pad, double* scale, cudaStream_t st);
+cudaError_t jb_tc05_slice_cols(const double* Rn, int64_t ldr, int64_t cols, int K, int S, int8_t* Rq,
+                               int64_t cols_pad, double* scale, const uint32_t* flags, uint32_t expect,
+                               cudaStream_t st);
+int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st);
+
 #include "kernels_formula.h"

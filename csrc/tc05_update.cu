@@ -1,0 +1,496 @@
+// K3b `trailing_update_tc05` — the trailing update C += L * (-R) on the 5th-generation tensor cores
+// (tcgen05.mma, accumulators in TMEM) with an error-free integer split of the fp64 operands
+// (Ozaki-style), optional path selected by JbConfig.precision = 1.
+//
+// Why integers and not a tf32 / bf16 split with fp32 accumulation: kappa_inf(|i-j|) ~ 1e9 at
+// n = 32768, so an fp32-accumulated elimination (eps ~ 6e-8) does not even give a convergent Newton
+// start.  tcgen05.mma kind::i8 accumulates exactly in int32, so with 7-bit signed digits
+//     L(i,k)  = 2^eL(i) * sum_s qL_s(i,k) 2^(-6-7s),   |qL_s| <= 64   (row scaling)
+//     -R(k,j) = 2^eR(j) * sum_u qR_u(k,j) 2^(-6-7u),   |qR_u| <= 64   (column scaling)
+// every slice product sum_k qL_s qR_u is exact, the pairs with s+u = d share one TMEM accumulator
+// (|D_d| < 2^23), and  L*(-R) = 2^(eL+eR-12) * sum_d D_d 2^(-7d)  is recombined in fp64 by the
+// epilogue.  S = 8 slices keep 55 bits below each row / column maximum, i.e. fp64-level accuracy.
+//
+// Kernel layout (1 CTA / SM, 192 threads): warp 0 = TMA producer (SWIZZLE_128B K-major int8 tiles),
+// warp 1 = TMEM allocator + single-thread MMA issuer (36 slice pairs x 4 K-steps per 128x64 tile),
+// warps 2-5 = epilogue (tcgen05.ld -> Horner recombination in fp64 -> C read-modify-write).
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include "common.cuh"
+#include "engine_types.h"
+#include "kernels.h"
+#include "../include/jordan_b200.h"
+
+using namespace jb;
+
+namespace {
+
+constexpr int TC_M = 128;      // rows per tile (UMMA M)
+constexpr int TC_N = 64;       // columns per tile (UMMA N); S accumulators x 64 columns = 512 TMEM columns
+constexpr int TC_K = 128;      // K per k-block = one 128-byte swizzle atom of int8
+constexpr int TC_SMAX = 8;     // slices
+constexpr int TC_THREADS = 192;
+constexpr int A_SLICE_BYTES = TC_M * TC_K;  // 16 KB
+constexpr int B_SLICE_BYTES = TC_N * TC_K;  // 8 KB
+
+// ---------------------------------------------------------------------------------------------
+// slicing kernels
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int exponent_of(double amax) {
+  // amax = f * 2^e with f in [0.5, 1)  ->  |x| < 2^e for every |x| <= amax
+  if (amax == 0.0) return 0;
+  const int hi = __double2hiint(amax);
+  return ((hi >> 20) & 0x7ff) - 1022;
+}
+__device__ __forceinline__ double pow2(int k) {  // 2^k for k in the normal range
+  return __hiloint2double((1023 + k) << 20, 0);
+}
+
+// one warp per row: L[rows][K] (ld = ldl) -> Lq[s][kb][row][128] int8, scale[row] = 2^(e-6)
+__global__ void __launch_bounds__(256) k_slice_rows(const double* __restrict__ L, int64_t ldl,
+                                                    int64_t rows, int K, int S, int8_t* __restrict__ Lq,
+                                                    int64_t rows_pad, double* __restrict__ scale) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const int KB = (K + TC_K - 1) / TC_K;
+  for (int64_t r = warp; r < rows; r += nwarps) {
+    double amax = 0.0;
+    for (int k = lane; k < K; k += 32) amax = fmax(amax, fabs(L[r * ldl + k]));
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+    const int e = exponent_of(amax);
+    if (lane == 0) scale[r] = pow2(e - 6);
+    const double up = pow2(6 - e);
+    for (int k = lane; k < KB * TC_K; k += 32) {
+      double t = (k < K) ? L[r * ldl + k] * up : 0.0;  // |t| < 64, exact
+      const int kb = k / TC_K, kk = k % TC_K;
+      for (int s = 0; s < S; ++s) {
+        const double q = rint(t);
+        Lq[(((int64_t)s * KB + kb) * rows_pad + r) * TC_K + kk] = (int8_t)(int)q;
+        t = (t - q) * 128.0;  // exact: |t - q| <= 0.5
+      }
+    }
+  }
+}
+
+// one thread per column: Rn[K][cols] (ld = ldr) -> Rq[s][kb][col][128] int8, scale[col] = 2^(e-6)
+__global__ void __launch_bounds__(128) k_slice_cols(const double* __restrict__ Rn, int64_t ldr,
+                                                    int64_t cols, int K, int S, int8_t* __restrict__ Rq,
+                                                    int64_t cols_pad, double* __restrict__ scale,
+                                                    const uint32_t* flags, uint32_t expect) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (flags) {  // wait until the pivot-row tile holding my column has landed (owner's SCALE)
+    if (threadIdx.x == 0) wait_flag_ge(flags + (blockIdx.x * blockDim.x) / JB_BN, expect);
+    __syncthreads();
+  }
+  if (j >= cols) return;
+  const int KB = (K + TC_K - 1) / TC_K;
+  double amax = 0.0;
+  for (int k = 0; k < K; ++k) amax = fmax(amax, fabs(Rn[(int64_t)k * ldr + j]));
+  const int e = exponent_of(amax);
+  scale[j] = pow2(e - 6);
+  const double up = pow2(6 - e);
+  for (int kb = 0; kb < KB; ++kb) {
+    for (int k16 = 0; k16 < TC_K; k16 += 16) {
+      double t[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int k = kb * TC_K + k16 + i;
+        t[i] = (k < K) ? Rn[(int64_t)k * ldr + j] * up : 0.0;
+      }
+      for (int s = 0; s < S; ++s) {
+        uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const double q = rint(t[i]);
+          w[i >> 2] |= ((uint32_t)(uint8_t)(int8_t)(int)q) << (8 * (i & 3));
+          t[i] = (t[i] - q) * 128.0;
+        }
+        uint4* dst = reinterpret_cast<uint4*>(Rq + (((int64_t)s * KB + kb) * cols_pad + j) * TC_K + k16);
+        *dst = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// tcgen05 helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, int x, int y, int z,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+      : "memory");
+}
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);          // start address
+  d |= (uint64_t)1 << 16;                              // leading byte offset (unused for K-major SW128)
+  d |= (uint64_t)(1024 >> 4) << 32;                    // stride byte offset: 8 rows x 128 B
+  d |= (uint64_t)1 << 46;                              // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                              // layout type SWIZZLE_128B
+  return d;
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u), "r"(0u), "r"(0u),
+      "r"(0u)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t* v) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+                 "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct Tc05Params {
+  double* C;              // rows x cols fp64, ld = ldc (updated in place)
+  int64_t ldc;
+  const double* rscale;   // [rows]  2^(eL-6)
+  const double* cscale;   // [cols]  2^(eR-6)
+  int64_t rows, cols;     // rows: multiple of 128
+  int KB, S;
+  int rt_count, ct_count; // tiles
+  // rows to skip (block row t / swapped-in row are handled by the fp64 kernel): [skip0, skip0+skiplen)
+  int64_t skip0, skiplen, skip1, skiplen1;
+  const JbCtl* ctl;       // optional: early-out when the matrix was found singular
+  const JbStepInfo* stepinfo;  // optional (engine): swapped-in row comes from stepinfo[t]
+  int t, m, rank;
+  int col_t0, col_t1;     // column slot t: accumulate from zero instead of C (engine only; -1 = none)
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_tc05_update(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
+              const __grid_constant__ CUtensorMap tmB) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t bar_full, bar_smem_free, bar_tmem_full, bar_tmem_free;
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ __align__(16) double cs_tile[2][TC_N];  // column scales of the tile in flight (bulk-copied)
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (P.ctl && P.ctl->singular) return;
+
+  // rows excluded from this kernel
+  int64_t skipA0 = P.skip0, skipA1 = P.skip0 + P.skiplen, skipB0 = P.skip1, skipB1 = P.skip1 + P.skiplen1;
+  if (P.stepinfo) {
+    const JbStepInfo si = P.stepinfo[P.t];
+    if (si.do_swap && si.piv_rank == P.rank) {
+      skipB0 = (int64_t)si.piv_slot * P.m;
+      skipB1 = skipB0 + P.m;
+    }
+  }
+
+  unsigned char* sA = smem;                                   // S slices x 16 KB
+  unsigned char* sB = smem + (size_t)P.S * A_SLICE_BYTES;     // S slices x 8 KB
+
+  if (tid == 0) {
+    mbar_init(&bar_full, 1);
+    mbar_init(&bar_smem_free, 1);
+    mbar_init(&bar_tmem_full, 1);
+    mbar_init(&bar_tmem_free, 4);  // one arrive per epilogue warp
+    mbar_fence_init();
+  }
+  if (warp == 1) {  // TMEM: all 512 columns (S accumulators of 64 columns)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+        smem_u32(&tmem_base_smem)), "r"(512u));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  const int total = P.rt_count * P.ct_count;
+  auto row_skipped = [&](int rt) {
+    const int64_t r0 = (int64_t)rt * TC_M;
+    return (r0 >= skipA0 && r0 < skipA1) || (r0 >= skipB0 && r0 < skipB1);
+  };
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      tma_prefetch_desc(&tmA);
+      tma_prefetch_desc(&tmB);
+      uint32_t n = 0, pitem = 0;
+      for (int idx = blockIdx.x; idx < total; idx += gridDim.x, ++pitem) {
+        const int rt = idx % P.rt_count, ct = idx / P.rt_count;
+        if (row_skipped(rt)) {
+          --pitem;
+          continue;
+        }
+        for (int kb = 0; kb < P.KB; ++kb, ++n) {
+          mbar_wait(&bar_smem_free, (n & 1) ^ 1);
+          mbar_expect_tx(&bar_full, (uint32_t)P.S * (A_SLICE_BYTES + B_SLICE_BYTES) +
+                                        (kb == 0 ? (uint32_t)(TC_N * 8) : 0u));
+          if (kb == 0) {
+            asm volatile(
+                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                ::"r"(smem_u32(&cs_tile[pitem & 1][0])), "l"(P.cscale + (int64_t)ct * TC_N),
+                "r"((uint32_t)(TC_N * 8)), "r"(smem_u32(&bar_full))
+                : "memory");
+          }
+          for (int s = 0; s < P.S; ++s) {
+            tma_load_3d(sA + (size_t)s * A_SLICE_BYTES, &tmA, 0, rt * TC_M, s * P.KB + kb, &bar_full);
+            tma_load_3d(sB + (size_t)s * B_SLICE_BYTES, &tmB, 0, ct * TC_N, s * P.KB + kb, &bar_full);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      // instruction descriptor: D = S32, A = B = signed int8, both K-major, N = 64, M = 128
+      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_N >> 3) << 17) |
+                             ((uint32_t)(TC_M >> 4) << 24);
+      const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+      uint32_t n = 0, item = 0;
+      for (int idx = blockIdx.x; idx < total; idx += gridDim.x) {
+        const int rt = idx % P.rt_count;
+        if (row_skipped(rt)) continue;
+        mbar_wait(&bar_tmem_free, (item & 1) ^ 1);  // epilogue has drained the accumulators
+        tc_fence_after();
+        for (int kb = 0; kb < P.KB; ++kb, ++n) {
+          mbar_wait(&bar_full, n & 1);
+          tc_fence_after();
+          for (int d = 0; d < P.S; ++d) {
+            for (int s = 0; s <= d; ++s) {
+              const int u = d - s;
+              const uint64_t ad = umma_desc_sw128(a0 + s * A_SLICE_BYTES);
+              const uint64_t bd = umma_desc_sw128(b0 + u * B_SLICE_BYTES);
+#pragma unroll
+              for (int k4 = 0; k4 < TC_K / 32; ++k4) {
+                // advance 32 bytes (one UMMA_K of int8) inside the 128-byte swizzle atom
+                umma_i8(tmem_base + d * TC_N, ad + (uint64_t)(k4 * 2), bd + (uint64_t)(k4 * 2), idesc,
+                        (kb > 0 || s > 0 || k4 > 0) ? 1u : 0u);
+              }
+            }
+          }
+          umma_commit(&bar_smem_free);  // operands consumed -> producer may refill
+        }
+        umma_commit(&bar_tmem_full);    // all MMAs of the tile retired -> epilogue
+        ++item;
+      }
+    }
+  } else {
+    // ===================================================================== epilogue warps 2..5
+    const int q = warp & 3;                      // TMEM lane quarter this warp may access
+    const int row_in_tile = q * 32 + lane;
+    uint32_t item = 0;
+    for (int idx = blockIdx.x; idx < total; idx += gridDim.x) {
+      const int rt = idx % P.rt_count, ct = idx / P.rt_count;
+      if (row_skipped(rt)) continue;
+      const int64_t r = (int64_t)rt * TC_M + row_in_tile;
+      const double rs = P.rscale[r];
+      double* crow = P.C + r * P.ldc;
+      const int64_t col0 = (int64_t)ct * TC_N;
+      // prefetch my 64 C values (512 contiguous bytes of one row) while the MMAs of this tile run;
+      // TMEM lanes are rows, so the thread <-> row mapping is fixed and every thread must hide its
+      // own DRAM latency
+      double2 cpre[TC_N / 2];
+#pragma unroll
+      for (int i = 0; i < TC_N / 2; ++i) {
+        const int64_t c = col0 + 2 * i;
+        double2 cv = make_double2(0.0, 0.0);
+        if (c < P.cols) cv = *reinterpret_cast<const double2*>(crow + c);
+        if (c >= P.col_t0 && c < P.col_t1) cv.x = 0.0;
+        if (c + 1 >= P.col_t0 && c + 1 < P.col_t1) cv.y = 0.0;
+        cpre[i] = cv;
+      }
+      mbar_wait(&bar_tmem_full, item & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c8 = 0; c8 < TC_N; c8 += 8) {
+        int32_t v[TC_SMAX][8];
+#pragma unroll
+        for (int d = 0; d < TC_SMAX; ++d) {
+          if (d < P.S) {
+            tmem_ld8(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(d * TC_N + c8), v[d]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[d][i] = 0;
+          }
+        }
+        tmem_wait_ld();
+        const int64_t col = col0 + c8;
+        if (col < P.cols) {
+          double out[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            double acc = 0.0;
+#pragma unroll
+            for (int d = TC_SMAX - 1; d >= 0; --d) acc = fma(acc, 0.0078125, (double)v[d][i]);  // * 2^-7
+            out[i] = acc;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            const int64_t c = col + i;
+            if (c < P.cols) {
+              double2 cv = cpre[(c8 + i) / 2];
+              cv.x = fma(out[i], rs * cs_tile[item & 1][c8 + i], cv.x);
+              cv.y = fma(out[i + 1], rs * cs_tile[item & 1][c8 + i + 1], cv.y);
+              *reinterpret_cast<double2*>(crow + c) = cv;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_tmem_free);
+      ++item;
+    }
+  }
+
+  // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u));
+  }
+}
+
+int make_map_i8(CUtensorMap* map, const void* base, uint64_t rows, uint64_t planes, uint32_t box_rows) {
+  typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      jb_set_error("cuTensorMapEncodeTiled entry point not available");
+      return JB_ERR_CUDA;
+    }
+    fn = (EncodeTiledFn)p;
+  }
+  cuuint64_t gdim[3] = {(cuuint64_t)TC_K, rows, planes};
+  cuuint64_t gstr[2] = {(cuuint64_t)TC_K, (cuuint64_t)TC_K * rows};
+  cuuint32_t box[3] = {(cuuint32_t)TC_K, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    jb_set_error("cuTensorMapEncodeTiled(int8) failed: %d", (int)r);
+    return JB_ERR_CUDA;
+  }
+  return JB_OK;
+}
+
+}  // namespace
+
+size_t jb_tc05_smem_bytes(int S) { return (size_t)S * (A_SLICE_BYTES + B_SLICE_BYTES); }
+
+// Workspace sizes for `rows` x K (left) and K x `cols` (right) operands.
+size_t jb_tc05_lq_bytes(int64_t rows_pad, int K, int S) {
+  return (size_t)S * ((K + TC_K - 1) / TC_K) * rows_pad * TC_K;
+}
+size_t jb_tc05_rq_bytes(int64_t cols_pad, int K, int S) {
+  return (size_t)S * ((K + TC_K - 1) / TC_K) * cols_pad * TC_K;
+}
+
+cudaError_t jb_tc05_slice_rows(const double* L, int64_t ldl, int64_t rows, int K, int S, int8_t* Lq,
+                               int64_t rows_pad, double* scale, cudaStream_t st) {
+  if (rows == 0) return cudaSuccess;
+  int grid = (int)std::min<int64_t>((rows + 7) / 8, 148 * 8);
+  k_slice_rows<<<grid, 256, 0, st>>>(L, ldl, rows, K, S, Lq, rows_pad, scale);
+  return cudaGetLastError();
+}
+
+cudaError_t jb_tc05_slice_cols(const double* Rn, int64_t ldr, int64_t cols, int K, int S, int8_t* Rq,
+                               int64_t cols_pad, double* scale, const uint32_t* flags, uint32_t expect,
+                               cudaStream_t st) {
+  if (cols == 0) return cudaSuccess;
+  int grid = (int)((cols + 127) / 128);
+  k_slice_cols<<<grid, 128, 0, st>>>(Rn, ldr, cols, K, S, Rq, cols_pad, scale, flags, expect);
+  return cudaGetLastError();
+}
+
+int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
+  CUtensorMap tmA, tmB;
+  const int KB = (a.K + TC_K - 1) / TC_K;
+  int rc = make_map_i8(&tmA, a.Lq, (uint64_t)a.rows_pad, (uint64_t)a.S * KB, TC_M);
+  if (rc) return rc;
+  rc = make_map_i8(&tmB, a.Rq, (uint64_t)a.cols_pad, (uint64_t)a.S * KB, TC_N);
+  if (rc) return rc;
+  Tc05Params P;
+  memset(&P, 0, sizeof(P));
+  P.C = a.C; P.ldc = a.ldc; P.rscale = a.rscale; P.cscale = a.cscale; P.rows = a.rows; P.cols = a.cols;
+  P.KB = KB; P.S = a.S; P.rt_count = (int)(a.rows / TC_M); P.ct_count = (int)((a.cols + TC_N - 1) / TC_N);
+  P.skip0 = a.skip0; P.skiplen = a.skiplen; P.skip1 = 0; P.skiplen1 = 0;
+  P.ctl = a.ctl; P.stepinfo = a.stepinfo; P.t = a.t; P.m = a.m; P.rank = a.rank;
+  P.col_t0 = a.col_t0; P.col_t1 = a.col_t1;
+  const size_t smem = jb_tc05_smem_bytes(a.S);
+  static bool configured[JB_MAX_RANKS] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev % JB_MAX_RANKS]) {
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)jb_tc05_smem_bytes(TC_SMAX)));
+    configured[dev % JB_MAX_RANKS] = true;
+  }
+  if (P.rt_count == 0 || P.ct_count == 0) return JB_OK;
+  k_tc05_update<<<a.grid, TC_THREADS, smem, st>>>(P, tmA, tmB);
+  JB_CHECK(cudaGetLastError());
+  return JB_OK;
+}
+
+// Stand-alone entry for tests / tools: C (rows x cols) += L (rows x K) * Rn (K x cols), all fp64 in
+// device memory, computed on the tcgen05 int8 path with S slices.  rows must be a multiple of 128.
+extern "C" int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t cols, const double* L,
+                                   int64_t ldl, const double* Rn, int64_t ldr, int32_t K, int32_t S,
+                                   void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (rows % TC_M != 0 || S < 1 || S > TC_SMAX || K < 1 || (ldc & 1) || cols < 1) {
+    jb_set_error("jb_tc05_gemm_update: rows must be a multiple of 128, 1 <= S <= 8, even ldc");
+    return JB_ERR_ARG;
+  }
+  const int64_t cols_pad = (cols + TC_N - 1) / TC_N * TC_N;
+  int8_t *Lq = nullptr, *Rq = nullptr;
+  double *rs = nullptr, *cs = nullptr;
+  JB_CHECK(cudaMalloc((void**)&Lq, jb_tc05_lq_bytes(rows, K, S)));
+  JB_CHECK(cudaMalloc((void**)&Rq, jb_tc05_rq_bytes(cols_pad, K, S)));
+  JB_CHECK(cudaMalloc((void**)&rs, (size_t)rows * 8));
+  JB_CHECK(cudaMalloc((void**)&cs, (size_t)cols_pad * 8));
+  JB_CHECK(cudaMemsetAsync(Rq, 0, jb_tc05_rq_bytes(cols_pad, K, S), st));
+  JB_CHECK(cudaMemsetAsync(cs, 0, (size_t)cols_pad * 8, st));
+  JB_CHECK(jb_tc05_slice_rows(L, ldl, rows, K, S, Lq, rows, rs, st));
+  JB_CHECK(jb_tc05_slice_cols(Rn, ldr, cols, K, S, Rq, cols_pad, cs, nullptr, 0, st));
+  Tc05Launch a;
+  memset(&a, 0, sizeof(a));
+  a.C = C; a.ldc = ldc; a.rows = rows; a.cols = cols; a.Lq = Lq; a.Rq = Rq; a.rows_pad = rows;
+  a.cols_pad = cols_pad; a.rscale = rs; a.cscale = cs; a.K = K; a.S = S; a.grid = 148;
+  a.col_t0 = -1; a.col_t1 = -1;
+  int rc = jb_tc05_launch(a, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(Lq); cudaFree(Rq); cudaFree(rs); cudaFree(cs);
+  if (rc) return rc;
+  JB_CHECK(e);
+  return JB_OK;
+}

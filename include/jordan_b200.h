@@ -121,6 +121,10 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
 /* stand-alone kernels for tests / tools */
 int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
                      double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
+/* C (rows x cols) += L (rows x K) * Rn (K x cols), fp64 operands in device memory, computed on the
+ * tcgen05 int8-split path (K3b) with S slices; rows must be a multiple of 128 (test / tool entry). */
+int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t cols, const double* L,
+                        int64_t ldl, const double* Rn, int64_t ldr, int32_t K, int32_t S, void* stream);
 /* Same operation for callers that must not allocate (all device memory already handed to a pool,
  * or no room for cudaMalloc's device-wide synchronisation).  No counterpart in the reference.
  * Staging lives in a fixed ~4 MiB device array inside the library (resident on every GPU that
