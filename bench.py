@@ -36,6 +36,7 @@ def parse_args():
     ap.add_argument("--n", type=int, default=int(os.environ.get("JB_BENCH_N", "32768")))
     ap.add_argument("--m", type=int, default=int(os.environ.get("JB_BENCH_M", "128")))
     ap.add_argument("--formula", type=int, default=1)
+    ap.add_argument("--precision", default=os.environ.get("JB_PRECISION", "fp64"), choices=["fp64", "tc05"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--residual", action="store_true", help="also compute ||AX-I|| after the timed region")
     return ap.parse_args()
@@ -60,7 +61,7 @@ def run_own(args) -> dict:
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
     n, m, W, K = args.n, args.m, max(args.warmup, 0), args.steps
-    s = JordanSolver(n, m, comm=comm, device=local_rank)
+    s = JordanSolver(n, m, comm=comm, device=local_rank, precision=args.precision)
     lay = s.layout
 
     def one_step():
@@ -134,7 +135,7 @@ def run_own(args) -> dict:
         "impl": "own",
         "config": {"model": "block Gauss-Jordan inverse, generator |i-j|", "n": n, "m": m,
                    "global_batch": 1, "seq_len": n, "parallelism": f"block-cyclic rows x{comm.world}",
-                   "flop_convention": "2n^3 (executed)", "symm": s.symm_mode,
+                   "flop_convention": "2n^3 (executed)", "symm": s.symm_mode, "update_path": args.precision,
                    "l2": "inputs (n^2*8 B per inversion) larger than L2; matrix regenerated every step"},
         "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": t_wall / max(K, 1) * 1e3,
         "e2e": e2e,

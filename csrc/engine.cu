@@ -80,6 +80,14 @@ struct JbEngine {
   cudaStream_t hstream = nullptr;        // high-priority stream running K1(t+1) beside step_B(t)
   cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr};
   bool lookahead = true;
+  // tcgen05 split-precision update (precision = 1)
+  bool tc05 = false;
+  int tc_slices = 8;
+  int8_t* Lq[2] = {nullptr, nullptr};
+  int8_t* Rq = nullptr;
+  double* rscale[2] = {nullptr, nullptr};
+  double* cscale = nullptr;
+  int64_t cols_pad = 0;
   int* okbuf = nullptr;
   JbCtl* ctl = nullptr;
   JbStepInfo* stepinfo = nullptr;
@@ -174,6 +182,22 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   if (r == cudaSuccess) r = dmalloc((void**)&e->rowsum, rl * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->scratch_max, 64);
   if (r == cudaSuccess && cfg->keep_copy) r = dmalloc((void**)&e->Acopy, rl * e->ldw * 8);
+  if (cfg->precision == 1) {
+    if (e->m % 128 != 0) {
+      jb_set_error("precision=1 (tcgen05 update) needs a block size that is a multiple of 128");
+      jb_engine_destroy(e);
+      return JB_ERR_ARG;
+    }
+    e->tc05 = true;
+    if (const char* sl = getenv("JB_TC05_SLICES")) e->tc_slices = std::max(1, std::min(8, atoi(sl)));
+    e->cols_pad = (e->ldw + 63) / 64 * 64;
+    for (int i = 0; i < 2 && r == cudaSuccess; ++i) {
+      r = dmalloc((void**)&e->Lq[i], jb_tc05_lq_bytes(rl, e->Kp, 8));
+      if (r == cudaSuccess) r = dmalloc((void**)&e->rscale[i], rl * 8);
+    }
+    if (r == cudaSuccess) r = dmalloc((void**)&e->Rq, jb_tc05_rq_bytes(e->cols_pad, e->Kp, 8));
+    if (r == cudaSuccess) r = dmalloc((void**)&e->cscale, (size_t)e->cols_pad * 8);
+  }
   if (r != cudaSuccess) {
     jb_set_error("Not enough memory! (%s)", cudaGetErrorString(r));  // main.cpp:375
     jb_engine_destroy(e);
@@ -226,6 +250,8 @@ void jb_engine_destroy(JbEngine* e) {
     if (e->evK[i]) cudaEventDestroy(e->evK[i]);
   }
   cudaFree(e->counters);
+  cudaFree(e->Lq[0]); cudaFree(e->Lq[1]); cudaFree(e->Rq); cudaFree(e->rscale[0]); cudaFree(e->rscale[1]);
+  cudaFree(e->cscale);
   cudaFree(e->W); cudaFree(e->Lbuf[0]); cudaFree(e->Lbuf[1]); cudaFree(e->invbuf); cudaFree(e->normbuf); cudaFree(e->okbuf);
   cudaFree(e->ctl); cudaFree(e->stepinfo); cudaFree(e->rowsum); cudaFree(e->scratch_max);
   cudaFree(e->Acopy); cudaFree(e->Xp); cudaFree(e->Rslab);
@@ -423,7 +449,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   }
   const uint32_t g0 = e->gstep;
   e->gstep += (uint32_t)e->Nr;
-  const bool la = e->lookahead && e->Nr > 1;
+  const bool la = e->lookahead && e->Nr > 1 && !e->tc05;
 
   // K1 of step t: candidates are the local block rows with global index >= t (main.cpp:1028)
   auto launch_k1 = [&](int64_t t, cudaStream_t s) -> cudaError_t {
@@ -436,7 +462,14 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     K.tag = g + 1;
     K.Lbuf = e->Lbuf[g & 1];
     e->launches += 1;
-    return jb_launch_k1(K, panel_ctas, s);
+    cudaError_t ce = jb_launch_k1(K, panel_ctas, s);
+    if (ce == cudaSuccess && e->tc05) {
+      // integer slices of the L panel for the tcgen05 update of this step
+      ce = jb_tc05_slice_rows(e->Lbuf[g & 1], e->Kp, e->rows_loc, e->m, e->tc_slices, e->Lq[g & 1],
+                              e->rows_loc, e->rscale[g & 1], s);
+      e->launches += 1;
+    }
+    return ce;
   };
   auto launch_step = [&](int64_t t, int phase, cudaStream_t s) -> cudaError_t {
     const uint32_t g = g0 + (uint32_t)t;
@@ -455,9 +488,35 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     // priority column tiles = the ones covering block column t+1 (what K1(t+1) reads)
     S.pct0 = (int)(((t + 1) * e->m) / JB_BN);
     S.pct1 = (int)std::min<int64_t>(e->CT - 1, ((t + 2) * e->m - 1) / JB_BN);
+    if (e->tc05) {  // no priority tiles: phase A = scale/broadcast/swap, phase B = all UPD tiles
+      S.pct0 = 0;
+      S.pct1 = -1;
+    }
     S.counter = e->counters + 2 * t + (phase == JB_PHASE_B ? 1 : 0);
+    S.only_swapped = (e->tc05 && phase == JB_PHASE_B) ? 1 : 0;
     e->launches += 1;
     return jb_launch_step(S, e->maps[par], grid, s);
+  };
+  // tcgen05 mode: phase B = slice the (negated) pivot row, int8 tensor-core update of every block
+  // row except row t and the swapped-in row, which stays on the fp64 kernel (only_swapped)
+  auto launch_tc05_b = [&](int64_t t, cudaStream_t s) -> int {
+    const uint32_t g = g0 + (uint32_t)t;
+    const int par = g & 1;
+    const double* rowbuf = (const double*)(e->symm_peers[e->rank] + e->off_rowbuf[par]);
+    const uint32_t* rowflag = (const uint32_t*)(e->symm_peers[e->rank] + e->off_rowflag[par]);
+    JB_CHECK(jb_tc05_slice_cols(rowbuf, e->ldw, e->ldw, e->m, e->tc_slices, e->Rq, e->cols_pad, e->cscale,
+                                rowflag, ((g >> 1) + 1) * (uint32_t)e->nsub, s));
+    Tc05Launch a;
+    memset(&a, 0, sizeof(a));
+    a.C = e->W; a.ldc = e->ldw; a.rows = e->rows_loc; a.cols = e->ldw; a.Lq = e->Lq[par]; a.Rq = e->Rq;
+    a.rows_pad = e->rows_loc; a.cols_pad = e->cols_pad; a.rscale = e->rscale[par]; a.cscale = e->cscale;
+    a.K = e->m; a.S = e->tc_slices; a.grid = e->sm_count;
+    a.skip0 = (t % e->p == e->rank) ? (t / e->p) * e->m : -1;
+    a.skiplen = (t % e->p == e->rank) ? e->m : 0;
+    a.ctl = e->ctl; a.stepinfo = e->stepinfo; a.t = (int)t; a.m = e->m; a.rank = e->rank;
+    a.col_t0 = (int)(t * e->m); a.col_t1 = (int)((t + 1) * e->m);
+    e->launches += 2;
+    return jb_tc05_launch(a, s);
   };
 
   JB_CHECK(launch_k1(0, st));
@@ -475,6 +534,16 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       JB_CHECK(launch_step(t, JB_PHASE_B, st));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
       JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
+    } else if (e->tc05) {
+      // A with an EMPTY priority range = scale + broadcast + swap only; then the tcgen05 update of
+      // everything, then the fp64 kernel for the swapped-in row (if any)
+      JB_CHECK(launch_step(t, JB_PHASE_A, st));
+      int rc5 = launch_tc05_b(t, st);
+      if (rc5) return rc5;
+      JB_CHECK(launch_step(t, JB_PHASE_B, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));
+      if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
     } else {
       JB_CHECK(launch_step(t, JB_PHASE_ALL, st));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));

@@ -47,6 +47,7 @@ struct StepParams {
   int phase;              // JB_PHASE_ALL / _A / _B (look-ahead split)
   int pct0, pct1;         // priority column tiles (cover block column t+1); empty if pct1 < pct0
   uint32_t* counter;      // work-item counter of THIS launch (zeroed by the host)
+  int only_swapped;       // phase B in tcgen05 mode: only the swapped-in block row stays on the fp64 path
 };
 enum { JB_PHASE_ALL = 0, JB_PHASE_A = 1, JB_PHASE_B = 2 };
 struct StepMaps {

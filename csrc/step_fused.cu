@@ -186,6 +186,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         if (idx >= pl.total) break;
         const Item it = decode(P, si, pl, idx);
         if (!kUpdOnly && it.type == IT_ROWT) continue;
+        if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;  // tcgen05 mode: the rest is done there
         const int col0 = it.ct * JB_BN;
         if (kUpdOnly || it.type != IT_SCALE) {
           wait_flag_ge(rowflag_local + it.ct, P.row_expect);  // pivot-row tile landed
@@ -230,6 +231,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
     if (idx >= pl.total) break;
     const Item it = decode(P, si, pl, idx);
     const int col0 = it.ct * JB_BN;
+    if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;
 
     if (!kUpdOnly && it.type == IT_ROWT) {
       // ---- K4: swap + install the scaled pivot row as block row t (one 64-row chunk per item).

@@ -45,7 +45,7 @@ class JordanSolver:
     """One instance per rank (= per GPU).  All ranks must call the collective methods together."""
 
     def __init__(self, n: int, m: int, comm: Optional[Comm] = None, device: Optional[int] = None,
-                 keep_copy: bool = False, symm: Optional[str] = None):
+                 keep_copy: bool = False, symm: Optional[str] = None, precision: str = "fp64"):
         if not torch.cuda.is_available():
             raise RuntimeError("JordanSolver needs a CUDA device; use models.eager.EagerJordan on CPU")
         self.lib = _native.cuda()
@@ -54,7 +54,10 @@ class JordanSolver:
         self.device = torch.cuda.current_device() if device is None else int(device)
         torch.cuda.set_device(self.device)
         self.formula: Optional[int] = None
-        cfg = _native.JbConfig(n, m, self.comm.world, self.comm.rank, self.device, int(keep_copy), 0)
+        # precision: "fp64" = DMMA update (default); "tc05" = tcgen05 int8 error-free split update (K3b)
+        self.precision = precision
+        cfg = _native.JbConfig(n, m, self.comm.world, self.comm.rank, self.device, int(keep_copy),
+                               {"fp64": 0, "tc05": 1}[precision])
         h = C.c_void_p()
         rc = self.lib.jb_engine_create(C.byref(cfg), C.byref(h))
         # collective allocation vote (main.cpp:371-381)

@@ -127,3 +127,36 @@ def test_refinement_reduces_residual():
     r1 = s.residual()
     assert r1 < r0 * 1e-2, (r0, r1)   # Newton-Schulz: quadratic contraction
     s.close()
+
+
+@pytest.mark.parametrize("fid,n,m", [(1, 1024, 128), (6, 1024, 128), (1, 768, 256), (5, 640, 128)])
+def test_tc05_update_path_matches_fp64_path(fid, n, m):
+    """K3b: the tcgen05 int8-split trailing update gives fp64-level results (same pivots, same X)."""
+    A = gen(fid, n)
+    Xo, piv = cpu_block_jordan(A, m, 1)
+    s = solver(n, m, precision="tc05")
+    s.fill_formula(fid)
+    s.invert()
+    X = s.local_inverse().cpu()
+    assert s.pivots() == piv
+    assert (X - Xo).abs().max() <= 1e-8 * Xo.abs().max()
+    r_tc = s.residual()
+    s.close()
+    f = solver(n, m)
+    f.fill_formula(fid)
+    f.invert()
+    r_64 = f.residual()
+    f.close()
+    assert r_tc <= 10 * r_64 + 1e-12, (r_tc, r_64)
+
+
+def test_tc05_gemm_building_block():
+    from mpi_jordan_crazy_acceleration_b200.ops import tc05_gemm_update
+
+    torch.manual_seed(0)
+    L = torch.randn(256, 128, dtype=torch.float64, device="cuda")
+    R = torch.randn(128, 192, dtype=torch.float64, device="cuda")
+    C0 = torch.randn(256, 192, dtype=torch.float64, device="cuda")
+    ref = C0 + L @ R
+    out = tc05_gemm_update(C0.clone(), L, R, 8)
+    assert ((out - ref).abs() / (L.abs() @ R.abs())).max() < 1e-13
