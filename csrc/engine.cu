@@ -83,10 +83,11 @@ struct JbEngine {
   // tcgen05 split-precision update (precision = 1)
   bool tc05 = false;
   int tc_slices = 8;
-  int8_t* Lq[2] = {nullptr, nullptr};
-  int8_t* Rq = nullptr;
-  double* rscale[2] = {nullptr, nullptr};
-  double* cscale = nullptr;
+  int8_t* Lq[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [step parity][k-block]
+  int8_t* Rq[2] = {nullptr, nullptr};                              // [k-block]
+  double* rscale[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  double* cscale[2] = {nullptr, nullptr};
+  int tc_kb = 1;
   int64_t cols_pad = 0;
   int* okbuf = nullptr;
   JbCtl* ctl = nullptr;
@@ -191,12 +192,20 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
     e->tc05 = true;
     if (const char* sl = getenv("JB_TC05_SLICES")) e->tc_slices = std::max(1, std::min(8, atoi(sl)));
     e->cols_pad = (e->ldw + 63) / 64 * 64;
-    for (int i = 0; i < 2 && r == cudaSuccess; ++i) {
-      r = dmalloc((void**)&e->Lq[i], jb_tc05_lq_bytes(rl, e->Kp, 8));
-      if (r == cudaSuccess) r = dmalloc((void**)&e->rscale[i], rl * 8);
+    e->tc_kb = (e->m + 127) / 128;
+    if (e->tc_kb > 2) {
+      jb_set_error("precision=1 supports m = 128 or 256");
+      jb_engine_destroy(e);
+      return JB_ERR_ARG;
     }
-    if (r == cudaSuccess) r = dmalloc((void**)&e->Rq, jb_tc05_rq_bytes(e->cols_pad, e->Kp, 8));
-    if (r == cudaSuccess) r = dmalloc((void**)&e->cscale, (size_t)e->cols_pad * 8);
+    for (int kb = 0; kb < e->tc_kb && r == cudaSuccess; ++kb) {
+      for (int i = 0; i < 2 && r == cudaSuccess; ++i) {
+        r = dmalloc((void**)&e->Lq[i][kb], jb_tc05_lq_bytes(rl, 128, 8));
+        if (r == cudaSuccess) r = dmalloc((void**)&e->rscale[i][kb], rl * 8);
+      }
+      if (r == cudaSuccess) r = dmalloc((void**)&e->Rq[kb], jb_tc05_rq_bytes(e->cols_pad, 128, 8));
+      if (r == cudaSuccess) r = dmalloc((void**)&e->cscale[kb], (size_t)e->cols_pad * 8);
+    }
   }
   if (r != cudaSuccess) {
     jb_set_error("Not enough memory! (%s)", cudaGetErrorString(r));  // main.cpp:375
@@ -250,8 +259,10 @@ void jb_engine_destroy(JbEngine* e) {
     if (e->evK[i]) cudaEventDestroy(e->evK[i]);
   }
   cudaFree(e->counters);
-  cudaFree(e->Lq[0]); cudaFree(e->Lq[1]); cudaFree(e->Rq); cudaFree(e->rscale[0]); cudaFree(e->rscale[1]);
-  cudaFree(e->cscale);
+  for (int i = 0; i < 2; ++i) {
+    for (int kb = 0; kb < 2; ++kb) { cudaFree(e->Lq[i][kb]); cudaFree(e->rscale[i][kb]); }
+    cudaFree(e->Rq[i]); cudaFree(e->cscale[i]);
+  }
   cudaFree(e->W); cudaFree(e->Lbuf[0]); cudaFree(e->Lbuf[1]); cudaFree(e->invbuf); cudaFree(e->normbuf); cudaFree(e->okbuf);
   cudaFree(e->ctl); cudaFree(e->stepinfo); cudaFree(e->rowsum); cudaFree(e->scratch_max);
   cudaFree(e->Acopy); cudaFree(e->Xp); cudaFree(e->Rslab);
@@ -465,9 +476,11 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     cudaError_t ce = jb_launch_k1(K, panel_ctas, s);
     if (ce == cudaSuccess && e->tc05) {
       // integer slices of the L panel for the tcgen05 update of this step
-      ce = jb_tc05_slice_rows(e->Lbuf[g & 1], e->Kp, e->rows_loc, e->m, e->tc_slices, e->Lq[g & 1],
-                              e->rows_loc, e->rscale[g & 1], s);
-      e->launches += 1;
+      for (int kb = 0; kb < e->tc_kb && ce == cudaSuccess; ++kb) {
+        ce = jb_tc05_slice_rows(e->Lbuf[g & 1] + kb * 128, e->Kp, e->rows_loc, std::min(128, e->m - kb * 128),
+                                e->tc_slices, e->Lq[g & 1][kb], e->rows_loc, e->rscale[g & 1][kb], s);
+        e->launches += 1;
+      }
     }
     return ce;
   };
@@ -504,19 +517,27 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     const int par = g & 1;
     const double* rowbuf = (const double*)(e->symm_peers[e->rank] + e->off_rowbuf[par]);
     const uint32_t* rowflag = (const uint32_t*)(e->symm_peers[e->rank] + e->off_rowflag[par]);
-    JB_CHECK(jb_tc05_slice_cols(rowbuf, e->ldw, e->ldw, e->m, e->tc_slices, e->Rq, e->cols_pad, e->cscale,
-                                rowflag, ((g >> 1) + 1) * (uint32_t)e->nsub, s));
-    Tc05Launch a;
-    memset(&a, 0, sizeof(a));
-    a.C = e->W; a.ldc = e->ldw; a.rows = e->rows_loc; a.cols = e->ldw; a.Lq = e->Lq[par]; a.Rq = e->Rq;
-    a.rows_pad = e->rows_loc; a.cols_pad = e->cols_pad; a.rscale = e->rscale[par]; a.cscale = e->cscale;
-    a.K = e->m; a.S = e->tc_slices; a.grid = e->sm_count;
-    a.skip0 = (t % e->p == e->rank) ? (t / e->p) * e->m : -1;
-    a.skiplen = (t % e->p == e->rank) ? e->m : 0;
-    a.ctl = e->ctl; a.stepinfo = e->stepinfo; a.t = (int)t; a.m = e->m; a.rank = e->rank;
-    a.col_t0 = (int)(t * e->m); a.col_t1 = (int)((t + 1) * e->m);
-    e->launches += 2;
-    return jb_tc05_launch(a, s);
+    for (int kb = 0; kb < e->tc_kb; ++kb) {
+      const int kk = std::min(128, e->m - kb * 128);
+      JB_CHECK(jb_tc05_slice_cols(rowbuf + (int64_t)kb * 128 * e->ldw, e->ldw, e->ldw, kk, e->tc_slices,
+                                  e->Rq[kb], e->cols_pad, e->cscale[kb], rowflag,
+                                  ((g >> 1) + 1) * (uint32_t)e->nsub, s));
+      Tc05Launch a;
+      memset(&a, 0, sizeof(a));
+      a.C = e->W; a.ldc = e->ldw; a.rows = e->rows_loc; a.cols = e->ldw; a.Lq = e->Lq[par][kb];
+      a.Rq = e->Rq[kb]; a.rows_pad = e->rows_loc; a.cols_pad = e->cols_pad; a.rscale = e->rscale[par][kb];
+      a.cscale = e->cscale[kb]; a.K = kk; a.S = e->tc_slices; a.grid = e->sm_count;
+      a.skip0 = (t % e->p == e->rank) ? (t / e->p) * e->m : -1;
+      a.skiplen = (t % e->p == e->rank) ? e->m : 0;
+      a.ctl = e->ctl; a.stepinfo = e->stepinfo; a.t = (int)t; a.m = e->m; a.rank = e->rank;
+      a.col_t0 = (int)(t * e->m); a.col_t1 = (int)((t + 1) * e->m);
+      a.zero_slot = (kb == 0);
+      if (kb > 0) { a.col_t0 = -1; a.col_t1 = -1; }  // v1: only the first k-block starts from zero
+      e->launches += 3;
+      int rc5 = jb_tc05_launch(a, s);
+      if (rc5) return rc5;
+    }
+    return JB_OK;
   };
 
   JB_CHECK(launch_k1(0, st));

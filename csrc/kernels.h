@@ -123,6 +123,7 @@ struct Tc05Launch {
   const JbStepInfo* stepinfo;
   int t, m, rank;
   int col_t0, col_t1;     // column slot t (accumulate from zero), -1/-1 = none
+  int zero_slot;          // v2: clear column slot t before this launch (first k-block only)
 };
 size_t jb_tc05_smem_bytes(int S);
 size_t jb_tc05_lq_bytes(int64_t rows_pad, int K, int S);

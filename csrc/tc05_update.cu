@@ -164,6 +164,10 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t* v) {
                : "r"(taddr)
                : "memory");
 }
+// exact int32 -> fp64 without I2F: bits(2^52 + (x + 2^31)) then subtract 2^52 + 2^31
+__device__ __forceinline__ double i32_to_f64(int x) {
+  return __hiloint2double(0x43300000, x ^ 0x80000000) - 4503601774854144.0;
+}
 __device__ __forceinline__ void tmem_wait_ld() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -182,6 +186,7 @@ struct Tc05Params {
   const JbStepInfo* stepinfo;  // optional (engine): swapped-in row comes from stepinfo[t]
   int t, m, rank;
   int col_t0, col_t1;     // column slot t: accumulate from zero instead of C (engine only; -1 = none)
+  int dbg;                // timing experiments only: 1 = no C store, 2 = plain store instead of reduce-add
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -373,6 +378,261 @@ k_tc05_update(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// v2: A slices resident per row tile, 128 x 32 column tiles, double-buffered TMEM accumulators and
+// B stages (MMA of tile i+1 overlaps the epilogue of tile i), and NO C traffic through the SM at
+// all: the epilogue writes the scaled fp64 tile into a SWIZZLE_128B staging buffer and one thread
+// issues a TMA reduce-add (cp.reduce.async.bulk.tensor ... .add, SASS UTMAREDG) that performs
+// C += tile in L2.  K is exactly one 128-byte k-block per launch (m = 256 -> two launches).
+// ---------------------------------------------------------------------------------------------
+constexpr int V2_N = 32;
+constexpr int V2_B_SLICE = V2_N * TC_K;              // 4 KB
+constexpr int V2_B_STAGE = TC_SMAX * V2_B_SLICE;     // 32 KB
+constexpr int V2_STG_HALF = TC_M * 16 * 8;           // 16 KB: 128 rows x 16 fp64 columns
+constexpr int V2_SMEM = TC_SMAX * A_SLICE_BYTES + 2 * V2_B_STAGE + 2 * V2_STG_HALF;  // 224 KB
+
+__device__ __forceinline__ int map_valid_rt(int vrt, int a0, int a1, int b0, int b1) {
+  int rt = vrt;
+  if (a1 > a0 && rt >= a0) rt += a1 - a0;
+  if (b1 > b0 && rt >= b0) rt += b1 - b0;
+  return rt;
+}
+
+template <int S_>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_tc05_update_v2(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
+                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmC) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t a_full, a_free, b_full[2], b_free[2], t_full[2], t_free[2];
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ __align__(16) double cs_tile[8][V2_N];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (P.ctl && P.ctl->singular) return;
+
+  // excluded row tiles (block row t; swapped-in row), as sorted, disjoint tile intervals
+  int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+  if (P.skiplen > 0) {
+    a0 = (int)(P.skip0 / TC_M);
+    a1 = (int)((P.skip0 + P.skiplen) / TC_M);
+  }
+  if (P.stepinfo) {
+    const JbStepInfo si = P.stepinfo[P.t];
+    if (si.do_swap && si.piv_rank == P.rank) {
+      b0 = (int)(((int64_t)si.piv_slot * P.m) / TC_M);
+      b1 = (int)(((int64_t)(si.piv_slot + 1) * P.m) / TC_M);
+    }
+  }
+  if (b1 > b0 && (a1 <= a0 || b0 < a0)) {  // order the intervals
+    int t0 = a0, t1 = a1;
+    a0 = b0; a1 = b1; b0 = t0; b1 = t1;
+  }
+  const int vrt_count = P.rt_count - (a1 - a0) - (b1 - b0);
+  const int64_t total = (int64_t)vrt_count * P.ct_count;
+  const int64_t lo = total * blockIdx.x / gridDim.x, hi = total * (blockIdx.x + 1) / gridDim.x;
+
+  unsigned char* sA = smem;
+  unsigned char* sB = smem + TC_SMAX * A_SLICE_BYTES;
+  unsigned char* sStg = sB + 2 * V2_B_STAGE;
+
+  if (tid == 0) {
+    mbar_init(&a_full, 1);
+    mbar_init(&a_free, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&b_full[i], 1);
+      mbar_init(&b_free[i], 1);
+      mbar_init(&t_full[i], 1);
+      mbar_init(&t_free[i], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+        smem_u32(&tmem_base_smem)), "r"(512u));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0 && lo < hi) {
+      tma_prefetch_desc(&tmA);
+      tma_prefetch_desc(&tmB);
+      int cur_rt = -1;
+      uint32_t na = 0, nb = 0;
+      for (int64_t idx = lo; idx < hi; ++idx, ++nb) {
+        const int vrt = (int)(idx / P.ct_count), ct = (int)(idx % P.ct_count);
+        const int rt = map_valid_rt(vrt, a0, a1, b0, b1);
+        if (rt != cur_rt) {
+          mbar_wait(&a_free, (na & 1) ^ 1);  // MMAs that read the previous A tile have retired
+          mbar_expect_tx(&a_full, (uint32_t)P.S * A_SLICE_BYTES);
+          for (int s = 0; s < P.S; ++s)
+            tma_load_3d(sA + (size_t)s * A_SLICE_BYTES, &tmA, 0, rt * TC_M, s, &a_full);
+          ++na;
+          cur_rt = rt;
+        }
+        const int st = nb & 1;
+        mbar_wait(&b_free[st], ((nb >> 1) & 1) ^ 1);
+        mbar_expect_tx(&b_full[st], (uint32_t)P.S * V2_B_SLICE + (uint32_t)(V2_N * 8));
+        for (int s = 0; s < P.S; ++s)
+          tma_load_3d(sB + (size_t)st * V2_B_STAGE + (size_t)s * V2_B_SLICE, &tmB, 0, ct * V2_N, s,
+                      &b_full[st]);
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+            ::"r"(smem_u32(&cs_tile[nb & 7][0])), "l"(P.cscale + (int64_t)ct * V2_N),
+            "r"((uint32_t)(V2_N * 8)), "r"(smem_u32(&b_full[st]))
+            : "memory");
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0 && lo < hi) {
+      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(V2_N >> 3) << 17) |
+                             ((uint32_t)(TC_M >> 4) << 24);
+      const uint32_t abase = smem_u32(sA), bbase = smem_u32(sB);
+      int cur_rt = -1;
+      uint32_t na = 0, nb = 0;
+      for (int64_t idx = lo; idx < hi; ++idx, ++nb) {
+        const int rt = map_valid_rt((int)(idx / P.ct_count), a0, a1, b0, b1);
+        if (rt != cur_rt) {
+          mbar_wait(&a_full, na & 1);
+          ++na;
+          cur_rt = rt;
+        }
+        const int tb = nb & 1, st = nb & 1;
+        mbar_wait(&t_free[tb], ((nb >> 1) & 1) ^ 1);  // epilogue drained this accumulator set
+        mbar_wait(&b_full[st], (nb >> 1) & 1);
+        tc_fence_after();
+        // The issue loop runs in ONE thread, so it must be straight-line code: S is a template
+        // parameter, all 36 x 4 descriptors are base + compile-time offsets (16-byte units), and the
+        // accumulate flags are constants.  (A rolled loop cost ~75 cycles of integer work per MMA
+        // against a 16-cycle MMA.)
+        const uint64_t adesc0 = umma_desc_sw128(abase);
+        const uint64_t bdesc0 = umma_desc_sw128(bbase + st * V2_B_STAGE);
+        const uint32_t dbase = tmem_base + tb * (TC_SMAX * V2_N);
+        if (P.dbg != 3)
+#pragma unroll
+        for (int d = 0; d < S_; ++d) {
+#pragma unroll
+          for (int s = 0; s <= d; ++s) {
+#pragma unroll
+            for (int k4 = 0; k4 < TC_K / 32; ++k4)
+              umma_i8(dbase + d * V2_N, adesc0 + (uint64_t)(s * (A_SLICE_BYTES / 16) + k4 * 2),
+                      bdesc0 + (uint64_t)((d - s) * (V2_B_SLICE / 16) + k4 * 2), idesc,
+                      (s > 0 || k4 > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&b_free[st]);
+        umma_commit(&t_full[tb]);
+        const bool last_of_rt =
+            (idx + 1 >= hi) || map_valid_rt((int)((idx + 1) / P.ct_count), a0, a1, b0, b1) != rt;
+        if (last_of_rt) umma_commit(&a_free);
+      }
+    }
+  } else {
+    // ===================================================================== epilogue warps 2..5
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const int ep_tid = tid - 64;
+    uint32_t nb = 0;
+    for (int64_t idx = lo; idx < hi; ++idx, ++nb) {
+      const int vrt = (int)(idx / P.ct_count), ct = (int)(idx % P.ct_count);
+      const int rt = map_valid_rt(vrt, a0, a1, b0, b1);
+      const int tb = nb & 1;
+      const double rs7 = P.rscale[(int64_t)rt * TC_M + row_in_tile] * 0.0078125;  // row scale * 2^-7
+      mbar_wait(&t_full[tb], (nb >> 1) & 1);
+      tc_fence_after();
+      const double* cs = cs_tile[nb & 7];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        unsigned char* stg = sStg + h * V2_STG_HALF;
+        // the reduce-store that read this staging half (two halves ago) must have finished reading
+        if (ep_tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        named_bar_sync(2, 128);
+#pragma unroll
+        for (int c8 = 0; c8 < 16; c8 += 8) {
+          int32_t v[TC_SMAX][8];
+#pragma unroll
+          for (int d = 0; d < TC_SMAX; ++d) {
+            if (d < P.S) {
+              tmem_ld8(tmem_base + ((uint32_t)(q * 32) << 16) +
+                           (uint32_t)(tb * (TC_SMAX * V2_N) + d * V2_N + h * 16 + c8), v[d]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[d][i] = 0;
+            }
+          }
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            // I2F.F64 runs at ~6-16 conversions/clk/SM on B200 (measured) and would dominate the
+            // epilogue, so: (1) adjacent diagonals are merged in int32 (|D_d| < 2^22, so
+            // D_2j * 128 + D_2j+1 fits), (2) int32 -> fp64 goes through the 2^52 magic constant
+            // (one LOP3 + one exact DADD on the full-rate FP64 pipe).
+            double o0 = 0.0, o1 = 0.0;
+            if (P.dbg != 4)
+#pragma unroll
+            for (int j = TC_SMAX / 2 - 1; j >= 0; --j) {
+              const int w0 = v[2 * j][i] * 128 + v[2 * j + 1][i];
+              const int w1 = v[2 * j][i + 1] * 128 + v[2 * j + 1][i + 1];
+              o0 = fma(o0, 6.103515625e-05, i32_to_f64(w0));  // * 2^-14
+              o1 = fma(o1, 6.103515625e-05, i32_to_f64(w1));
+            }
+            o0 *= rs7 * cs[h * 16 + c8 + i];
+            o1 *= rs7 * cs[h * 16 + c8 + i + 1];
+            const int chunk = ((c8 + i) >> 1) ^ (row_in_tile & 7);  // SWIZZLE_128B
+            *reinterpret_cast<double2*>(stg + row_in_tile * 128 + chunk * 16) = make_double2(o0, o1);
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        named_bar_sync(3, 128);
+        if (ep_tid == 0 && P.dbg == 2) {
+          asm volatile(
+              "cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];"
+              ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(ct * V2_N + h * 16), "r"(rt * TC_M),
+              "r"(smem_u32(stg))
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        } else if (ep_tid == 0 && P.dbg != 1) {
+          asm volatile(
+              "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+              ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(ct * V2_N + h * 16), "r"(rt * TC_M),
+              "r"(smem_u32(stg))
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&t_free[tb]);
+    }
+    if (ep_tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u));
+  }
+}
+
+// W(r, col0 .. col0+ncols) = 0 for every local row outside [skip0, skip0+skiplen): in the in-place
+// elimination column slot t starts from the identity column, and the v2 kernel only ever adds.
+__global__ void __launch_bounds__(256) k_zero_cols(double* W, int64_t ldw, int64_t rows, int64_t col0,
+                                                   int ncols, int64_t skip0, int64_t skiplen,
+                                                   const JbCtl* ctl) {
+  if (ctl && ctl->singular) return;
+  for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
+    if (r >= skip0 && r < skip0 + skiplen) continue;
+    for (int c = threadIdx.x; c < ncols; c += blockDim.x) W[r * ldw + col0 + c] = 0.0;
+  }
+}
+
+int make_map_f64_sw128(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t ld);
+
 int make_map_i8(CUtensorMap* map, const void* base, uint64_t rows, uint64_t planes, uint32_t box_rows) {
   typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                     const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -403,8 +663,37 @@ int make_map_i8(CUtensorMap* map, const void* base, uint64_t rows, uint64_t plan
   return JB_OK;
 }
 
+int make_map_f64_sw128(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t ld) {
+  typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess) {
+    jb_set_error("cuTensorMapEncodeTiled entry point not available");
+    return JB_ERR_CUDA;
+  }
+  EncodeTiledFn fn = (EncodeTiledFn)p;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 8};
+  cuuint32_t box[2] = {16, (cuuint32_t)TC_M};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    jb_set_error("cuTensorMapEncodeTiled(fp64 C) failed: %d", (int)r);
+    return JB_ERR_CUDA;
+  }
+  return JB_OK;
+}
+
 }  // namespace
 
+namespace {
+}
 size_t jb_tc05_smem_bytes(int S) { return (size_t)S * (A_SLICE_BYTES + B_SLICE_BYTES); }
 
 // Workspace sizes for `rows` x K (left) and K x `cols` (right) operands.
@@ -432,31 +721,57 @@ cudaError_t jb_tc05_slice_cols(const double* Rn, int64_t ldr, int64_t cols, int 
   return cudaGetLastError();
 }
 
+// One K <= 128 block: C += Lq * Rq with the scales of that block.  version 2 (default): resident-A,
+// TMA reduce-add epilogue; the caller has zeroed column slot t beforehand (k_zero_cols).
 int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
-  CUtensorMap tmA, tmB;
-  const int KB = (a.K + TC_K - 1) / TC_K;
-  int rc = make_map_i8(&tmA, a.Lq, (uint64_t)a.rows_pad, (uint64_t)a.S * KB, TC_M);
+  static const bool use_v1 = getenv("JB_TC05_V1") != nullptr;
+  CUtensorMap tmA, tmB, tmC;
+  int rc = make_map_i8(&tmA, a.Lq, (uint64_t)a.rows_pad, (uint64_t)a.S, TC_M);
   if (rc) return rc;
-  rc = make_map_i8(&tmB, a.Rq, (uint64_t)a.cols_pad, (uint64_t)a.S * KB, TC_N);
+  rc = make_map_i8(&tmB, a.Rq, (uint64_t)a.cols_pad, (uint64_t)a.S, use_v1 ? TC_N : V2_N);
   if (rc) return rc;
   Tc05Params P;
   memset(&P, 0, sizeof(P));
   P.C = a.C; P.ldc = a.ldc; P.rscale = a.rscale; P.cscale = a.cscale; P.rows = a.rows; P.cols = a.cols;
-  P.KB = KB; P.S = a.S; P.rt_count = (int)(a.rows / TC_M); P.ct_count = (int)((a.cols + TC_N - 1) / TC_N);
+  P.KB = 1; P.S = a.S; P.rt_count = (int)(a.rows / TC_M);
   P.skip0 = a.skip0; P.skiplen = a.skiplen; P.skip1 = 0; P.skiplen1 = 0;
   P.ctl = a.ctl; P.stepinfo = a.stepinfo; P.t = a.t; P.m = a.m; P.rank = a.rank;
   P.col_t0 = a.col_t0; P.col_t1 = a.col_t1;
-  const size_t smem = jb_tc05_smem_bytes(a.S);
+  if (const char* d = getenv("JB_TC05_DBG")) P.dbg = atoi(d);
   static bool configured[JB_MAX_RANKS] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev % JB_MAX_RANKS]) {
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)jb_tc05_smem_bytes(TC_SMAX)));
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
     configured[dev % JB_MAX_RANKS] = true;
   }
-  if (P.rt_count == 0 || P.ct_count == 0) return JB_OK;
-  k_tc05_update<<<a.grid, TC_THREADS, smem, st>>>(P, tmA, tmB);
+  if (P.rt_count == 0 || a.cols == 0) return JB_OK;
+  if (use_v1) {
+    P.ct_count = (int)((a.cols + TC_N - 1) / TC_N);
+    k_tc05_update<<<a.grid, TC_THREADS, jb_tc05_smem_bytes(a.S), st>>>(P, tmA, tmB);
+  } else {
+    rc = make_map_f64_sw128(&tmC, a.C, (uint64_t)a.cols, (uint64_t)a.rows, (uint64_t)a.ldc);
+    if (rc) return rc;
+    P.ct_count = (int)((a.cols + V2_N - 1) / V2_N);
+    // column slot t: the v2 epilogue only adds, so the slot is cleared first
+    if (a.col_t1 > a.col_t0 && a.zero_slot) {
+      int grid = (int)std::min<int64_t>(a.rows, 148 * 8);
+      k_zero_cols<<<grid, 256, 0, st>>>(a.C, a.ldc, a.rows, a.col_t0, a.col_t1 - a.col_t0, a.skip0,
+                                       a.skiplen, a.ctl);
+      JB_CHECK(cudaGetLastError());
+    }
+    if (a.S == 8) k_tc05_update_v2<8><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
+    else if (a.S == 7) k_tc05_update_v2<7><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
+    else if (a.S == 6) k_tc05_update_v2<6><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
+    else {
+      jb_set_error("tcgen05 update v2 is built for 6, 7 or 8 slices (got %d); set JB_TC05_V1=1 for others", a.S);
+      return JB_ERR_ARG;
+    }
+  }
   JB_CHECK(cudaGetLastError());
   return JB_OK;
 }
@@ -467,27 +782,32 @@ extern "C" int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t
                                    int64_t ldl, const double* Rn, int64_t ldr, int32_t K, int32_t S,
                                    void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  if (rows % TC_M != 0 || S < 1 || S > TC_SMAX || K < 1 || (ldc & 1) || cols < 1) {
+  if (rows % TC_M != 0 || S < 1 || S > TC_SMAX || K < 1 || (ldc & 1) || cols < 1 ||
+      (reinterpret_cast<uintptr_t>(C) & 15)) {
     jb_set_error("jb_tc05_gemm_update: rows must be a multiple of 128, 1 <= S <= 8, even ldc");
     return JB_ERR_ARG;
   }
   const int64_t cols_pad = (cols + TC_N - 1) / TC_N * TC_N;
   int8_t *Lq = nullptr, *Rq = nullptr;
   double *rs = nullptr, *cs = nullptr;
-  JB_CHECK(cudaMalloc((void**)&Lq, jb_tc05_lq_bytes(rows, K, S)));
-  JB_CHECK(cudaMalloc((void**)&Rq, jb_tc05_rq_bytes(cols_pad, K, S)));
+  JB_CHECK(cudaMalloc((void**)&Lq, jb_tc05_lq_bytes(rows, TC_K, S)));
+  JB_CHECK(cudaMalloc((void**)&Rq, jb_tc05_rq_bytes(cols_pad, TC_K, S)));
   JB_CHECK(cudaMalloc((void**)&rs, (size_t)rows * 8));
   JB_CHECK(cudaMalloc((void**)&cs, (size_t)cols_pad * 8));
-  JB_CHECK(cudaMemsetAsync(Rq, 0, jb_tc05_rq_bytes(cols_pad, K, S), st));
-  JB_CHECK(cudaMemsetAsync(cs, 0, (size_t)cols_pad * 8, st));
-  JB_CHECK(jb_tc05_slice_rows(L, ldl, rows, K, S, Lq, rows, rs, st));
-  JB_CHECK(jb_tc05_slice_cols(Rn, ldr, cols, K, S, Rq, cols_pad, cs, nullptr, 0, st));
-  Tc05Launch a;
-  memset(&a, 0, sizeof(a));
-  a.C = C; a.ldc = ldc; a.rows = rows; a.cols = cols; a.Lq = Lq; a.Rq = Rq; a.rows_pad = rows;
-  a.cols_pad = cols_pad; a.rscale = rs; a.cscale = cs; a.K = K; a.S = S; a.grid = 148;
-  a.col_t0 = -1; a.col_t1 = -1;
-  int rc = jb_tc05_launch(a, st);
+  int rc = JB_OK;
+  for (int k0 = 0; k0 < K && rc == JB_OK; k0 += TC_K) {  // one 128-wide k-block at a time
+    const int kb = std::min(TC_K, K - k0);
+    JB_CHECK(cudaMemsetAsync(Rq, 0, jb_tc05_rq_bytes(cols_pad, TC_K, S), st));
+    JB_CHECK(cudaMemsetAsync(cs, 0, (size_t)cols_pad * 8, st));
+    JB_CHECK(jb_tc05_slice_rows(L + k0, ldl, rows, kb, S, Lq, rows, rs, st));
+    JB_CHECK(jb_tc05_slice_cols(Rn + (int64_t)k0 * ldr, ldr, cols, kb, S, Rq, cols_pad, cs, nullptr, 0, st));
+    Tc05Launch a;
+    memset(&a, 0, sizeof(a));
+    a.C = C; a.ldc = ldc; a.rows = rows; a.cols = cols; a.Lq = Lq; a.Rq = Rq; a.rows_pad = rows;
+    a.cols_pad = cols_pad; a.rscale = rs; a.cscale = cs; a.K = kb; a.S = S; a.grid = 148;
+    a.col_t0 = -1; a.col_t1 = -1;
+    rc = jb_tc05_launch(a, st);
+  }
   cudaError_t e = cudaStreamSynchronize(st);
   cudaFree(Lq); cudaFree(Rq); cudaFree(rs); cudaFree(cs);
   if (rc) return rc;

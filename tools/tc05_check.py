@@ -3,7 +3,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from mpi_jordan_crazy_acceleration_b200.ops import tc05_gemm_update
 torch.manual_seed(0)
-for rows, cols, K, S in [(128, 64, 128, 8), (256, 192, 128, 8), (1024, 1000, 128, 8), (512, 512, 256, 8), (512, 512, 128, 4), (4096, 4096, 128, 8)]:
+for rows, cols, K, S in [(128, 64, 128, 8), (256, 192, 128, 8), (1024, 1000, 128, 8), (512, 512, 256, 8), (512, 512, 128, 6), (4096, 4096, 128, 8)]:
     L = torch.randn(rows, K, dtype=torch.float64, device="cuda") * torch.exp(3 * torch.randn(rows, 1, dtype=torch.float64, device="cuda"))
     R = torch.randn(K, cols, dtype=torch.float64, device="cuda")
     C0 = torch.randn(rows, cols + (cols % 2), dtype=torch.float64, device="cuda")[:, :cols]
