@@ -98,8 +98,9 @@ struct JbEngine {
   unsigned char* symm_peers[JB_MAX_RANKS] = {nullptr};
   unsigned char* symm_mc = nullptr;
   bool own_symm = false, symm_ready = false;
-  bool peers_opened[2] = {false, false};
+  bool peers_opened[3] = {false, false, false};
   const double* W_peers[JB_MAX_RANKS] = {nullptr};
+  const double* R_peers[JB_MAX_RANKS] = {nullptr};  // refinement residual slabs (K7)
   StepMaps maps[2];
   bool maps_ready = false;
   uint32_t gstep = 0;  // global step counter (same on every rank)
@@ -245,11 +246,12 @@ void jb_engine_destroy(JbEngine* e) {
   if (!e) return;
   cudaSetDevice(e->cfg.device);
   cudaDeviceSynchronize();
-  for (int which = 0; which < 2; ++which)
+  for (int which = 0; which < 3; ++which)
     if (e->peers_opened[which])
       for (int r = 0; r < e->p; ++r)
         if (r != e->rank) {
-          void* ptr = which == 0 ? (void*)e->symm_peers[r] : (void*)e->W_peers[r];
+          void* ptr = which == 0 ? (void*)e->symm_peers[r]
+                                 : (which == 1 ? (void*)e->W_peers[r] : (void*)e->R_peers[r]);
           if (ptr) cudaIpcCloseMemHandle(ptr);
         }
   if (e->own_symm && e->symm_peers[e->rank]) cudaFree(e->symm_peers[e->rank]);
@@ -305,7 +307,16 @@ int jb_engine_bind_symm(JbEngine* e, void* const* peer_ptrs, void* multicast_ptr
 int jb_engine_ipc_handle(JbEngine* e, int which, void* handle64) {
   JB_CHECK(cudaSetDevice(e->cfg.device));
   cudaIpcMemHandle_t h;
-  void* ptr = which == 0 ? (void*)e->symm_peers[e->rank] : (void*)e->W;
+  if (which == 2 && !e->Rslab) {  // refinement slabs are allocated on first use
+    const size_t slab = (size_t)std::max<int64_t>(e->rows_loc, 1) * e->ldw * 8;
+    if (cudaMalloc((void**)&e->Rslab, 2 * slab) != cudaSuccess) {
+      jb_set_error("Not enough memory! (refinement slabs)");
+      return JB_ERR_NOMEM;
+    }
+    JB_CHECK(cudaMemset(e->Rslab, 0, 2 * slab));
+    e->R_peers[e->rank] = e->Rslab;
+  }
+  void* ptr = which == 0 ? (void*)e->symm_peers[e->rank] : (which == 1 ? (void*)e->W : (void*)e->Rslab);
   if (!ptr) {
     jb_set_error("jb_engine_ipc_handle: region %d not allocated", which);
     return JB_ERR_ARG;
@@ -325,7 +336,8 @@ int jb_engine_open_peers(JbEngine* e, int which, const void* handles) {
     void* ptr = nullptr;
     JB_CHECK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
     if (which == 0) e->symm_peers[r] = (unsigned char*)ptr;
-    else e->W_peers[r] = (const double*)ptr;
+    else if (which == 1) e->W_peers[r] = (const double*)ptr;
+    else e->R_peers[r] = (const double*)ptr;
   }
   e->peers_opened[which] = true;
   if (which == 0) {
@@ -709,13 +721,14 @@ int jb_engine_residual(JbEngine* e, int formula, double* out_local, void* stream
   return JB_OK;
 }
 
-// Newton-Schulz refinement X <- X + X (I - A X), split in two collective phases so the caller can
-// place a cross-rank barrier between them:
-//   phase 0: Rslab = I - A X         (right operand X gathered from all ranks)
-//   phase 1: X    = X + X * R        (right operand R gathered from all ranks' Rslab)
-// Peer access to Rslab goes through the same IPC mapping as W: Rslab lives in the second half of
-// nothing shared, so phase 1 is only available for p == 1 unless W_peers-style handles for Rslab
-// were exchanged by the caller (see python parallel/comm.py which does that for p > 1).
+// Newton-Schulz refinement X <- X + X (I - A X) in fp64 (K7), split in two collective phases so the
+// caller can place the cross-rank barriers:
+//   phase 0: Rslab = I - A X       (right operand X pulled from every rank's W)
+//   -- barrier --
+//   phase 1: X = X + X * R         (right operand R pulled from every rank's Rslab)
+//   -- barrier --
+// For p > 1 exchange the IPC handles of the residual slabs first (jb_engine_ipc_handle /
+// jb_engine_open_peers with which = 2).
 int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream) {
   JB_CHECK(cudaSetDevice(e->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
@@ -726,13 +739,15 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream) {
       return JB_ERR_NOMEM;
     }
     JB_CHECK(cudaMemset(e->Rslab, 0, 2 * slab));
+    e->R_peers[e->rank] = e->Rslab;
   }
+  for (int r = 0; r < e->p; ++r)
+    if (!e->W_peers[r] || !e->R_peers[r]) {
+      jb_set_error("jb_engine_refine_phase: peer slabs not opened (which = 1 and which = 2)");
+      return JB_ERR_ARG;
+    }
   double* R = e->Rslab;
   double* Xnew = e->Rslab + slab / 8;
-  if (e->p != 1) {
-    jb_set_error("jb_engine_refine_phase: multi-rank refinement is driven from the Python layer");
-    return JB_ERR_ARG;
-  }
   const double* left = formula < 0 ? e->Acopy : nullptr;
   if (formula < 0 && !left) {
     jb_set_error("jb_engine_refine_phase: no kept copy of A");
@@ -741,9 +756,7 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream) {
   if (phase == 0) {
     return panel_gemm(e, e->W_peers, left, formula, JB_GEMM_STORE_R, R, nullptr, st);
   } else {
-    const double* rp[JB_MAX_RANKS] = {nullptr};
-    rp[0] = R;
-    int rc = panel_gemm(e, rp, e->W, 0, JB_GEMM_XPLUS, Xnew, e->W, st);
+    int rc = panel_gemm(e, e->R_peers, e->W, 0, JB_GEMM_XPLUS, Xnew, e->W, st);
     if (rc) return rc;
     JB_CHECK(cudaMemcpyAsync(e->W, Xnew, slab, cudaMemcpyDeviceToDevice, st));
     return JB_OK;

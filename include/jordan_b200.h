@@ -81,7 +81,8 @@ void jb_engine_destroy(JbEngine* e);
 size_t jb_engine_symm_bytes(const JbEngine* e);
 int jb_engine_alloc_symm(JbEngine* e);
 int jb_engine_bind_symm(JbEngine* e, void* const* peer_ptrs, void* multicast_ptr);
-/* which: 0 = symmetric region, 1 = matrix slab W.  handle: 64 bytes (cudaIpcMemHandle_t). */
+/* which: 0 = symmetric region, 1 = matrix slab W, 2 = refinement residual slab.
+ * handle: 64 bytes (cudaIpcMemHandle_t). */
 int jb_engine_ipc_handle(JbEngine* e, int which, void* handle64);
 int jb_engine_open_peers(JbEngine* e, int which, const void* handles /* p * 64 bytes */);
 /* Zero flags / mailboxes / step counter.  Call on all ranks, then barrier, e.g. after a singular
@@ -115,7 +116,8 @@ int jb_engine_download(JbEngine* e, int which /*0 = X (W), 1 = kept copy of A*/,
                        int64_t nrows, int64_t col0, int64_t ncols, double* host, int64_t ldh);
 /* local max_i sum_j |(A X - I)_ij| over this rank's rows; formula < 0 -> use the kept copy. */
 int jb_engine_residual(JbEngine* e, int formula, double* out_local, void* stream);
-/* one Newton step X <- X + X (I - A X) in fp64 (K7). Collective: barrier before and after. */
+/* Newton-Schulz X <- X + X (I - A X) in fp64 (K7): phase 0 = residual slab, barrier, phase 1 =
+ * update, barrier. */
 int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
 
 /* stand-alone kernels for tests / tools */

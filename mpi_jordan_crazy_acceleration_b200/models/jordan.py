@@ -254,12 +254,23 @@ class JordanSolver:
         return self.comm.allreduce_max(loc.value)
 
     def refine(self, steps: int = 1) -> None:
-        """K7 Newton-Schulz refinement ``X <- X + X (I - A X)`` in fp64 (single-rank for now)."""
+        """K7 Newton-Schulz refinement ``X <- X + X (I - A X)`` in fp64, collective over all ranks."""
         fid = -1 if self.formula is None else self.formula
+        if self.comm.world > 1 and not getattr(self, "_r_peers_open", False):
+            buf = C.create_string_buffer(64)
+            _native.check(self.lib.jb_engine_ipc_handle(self._h, 2, buf))
+            allh = b"".join(self.comm.allgather_bytes(buf.raw))
+            _native.check(self.lib.jb_engine_open_peers(self._h, 2, allh))
+            self._r_peers_open = True
         for _ in range(steps):
+            torch.cuda.synchronize()
+            self.comm.barrier()  # X is final everywhere
             _native.check(self.lib.jb_engine_refine_phase(self._h, fid, 0, self._stream()))
+            torch.cuda.synchronize()
+            self.comm.barrier()  # every residual slab is complete before anybody pulls it
             _native.check(self.lib.jb_engine_refine_phase(self._h, fid, 1, self._stream()))
-        torch.cuda.synchronize()
+            torch.cuda.synchronize()
+            self.comm.barrier()
 
     def set_profiling(self, on: bool = True) -> None:
         _native.check(self.lib.jb_engine_set_profiling(self._h, int(on)))

@@ -60,6 +60,29 @@ def main():
         ref = torch.linalg.inv(formula_rows(1, 64, torch.arange(64)))
         results.append({"case": "singular+recover", "ok": bool(sing and (X - ref).abs().max() < 1e-9)})
     s.close()
+    # K7 refinement across ranks: damage X, one Newton step must contract the residual quadratically
+    s = JordanSolver(512, 64, comm=comm, device=dev, symm=mode)
+    s.fill_formula(1)
+    s.invert()
+    X = s.local_inverse()
+    X += 1e-9 * torch.randn_like(X)
+    r0 = s.residual()
+    s.refine(1)
+    r1 = s.residual()
+    if comm.rank == 0:
+        results.append({"case": "refine", "r0": r0, "r1": r1, "ok": bool(r1 < 1e-2 * r0)})
+    s.close()
+    # tcgen05 update path across ranks
+    s = JordanSolver(1024, 128, comm=comm, device=dev, symm=mode, precision="tc05")
+    s.fill_formula(6)
+    s.invert()
+    X = s.gather_inverse()
+    piv = s.pivots()
+    if comm.rank == 0:
+        A = formula_rows(6, 1024, torch.arange(1024))
+        Xo, pivo = cpu_block_jordan(A, 128, p)
+        results.append({"case": "tc05", "ok": bool(piv == pivo and float((X - Xo).abs().max() / Xo.abs().max()) < 1e-8)})
+    s.close()
     if comm.rank == 0:
         print("MPRESULT " + json.dumps(results), flush=True)
     comm.barrier()
