@@ -123,6 +123,9 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
 /* stand-alone kernels for tests / tools */
 int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
                      double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
+/* Message-passing litmus between two peer GPUs of this process (payload stores, fence,
+ * st.release.sys flag / ld.acquire.sys spin): counts ordering violations over `iters` epochs. */
+int jb_flag_litmus(int dev_producer, int dev_consumer, int iters, unsigned long long* errors_out);
 /* C (rows x cols) += L (rows x K) * Rn (K x cols), fp64 operands in device memory, computed on the
  * tcgen05 int8-split path (K3b) with S slices; rows must be a multiple of 128 (test / tool entry). */
 int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t cols, const double* L,

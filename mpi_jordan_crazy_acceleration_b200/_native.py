@@ -105,6 +105,7 @@ def _declare_cuda(lib) -> None:
         "jb_engine_residual": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), vp]),
         "jb_engine_refine_phase": (C.c_int, [vp, C.c_int, C.c_int, vp]),
         "jb_block_inverse": (C.c_int, [vp, i64, i32, C.c_double, vp, vp, vp, vp]),
+        "jb_flag_litmus": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ulonglong)]),
         "jb_tc05_gemm_update": (C.c_int, [vp, i64, i64, i64, vp, i64, vp, i64, i32, i32, vp]),
     }
     for name, (res, args) in sig.items():

@@ -31,3 +31,17 @@ def test_multi_gpu_matches_oracle(mode):
     bad = [r for r in res if not r.get("ok", True)]
     assert not bad, bad
     assert any(r.get("swaps", 0) > 0 for r in res)  # the P2P block-row swap path was exercised
+
+
+def test_flag_protocol_litmus_two_gpus():
+    """Race detection for the release/acquire flag protocol used by every cross-GPU exchange."""
+    import ctypes as C
+
+    from mpi_jordan_crazy_acceleration_b200 import _native
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    errs = C.c_ulonglong(123)
+    for a, b in ((0, 1), (1, 0)):
+        _native.check(_native.cuda().jb_flag_litmus(a, b, 200000, C.byref(errs)))
+        assert errs.value == 0
