@@ -174,7 +174,7 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   if (r == cudaSuccess) r = dmalloc((void**)&e->W, rl * e->ldw * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[0], (rl + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[1], (rl + JB_BM) * e->Kp * 8);
-  if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(2 * e->Nr + 2) * 4);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(3 * e->Nr + 3) * 4);
   if (r == cudaSuccess)
     r = dmalloc((void**)&e->invbuf, ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->normbuf, (size_t)std::max(e->rloc, 1) * 8);
@@ -447,7 +447,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   JB_CHECK(cudaMemsetAsync(e->ctl, 0, offsetof(JbCtl, norm_a), st));
 
-  JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(2 * e->Nr + 2) * 4, st));
+  JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(3 * e->Nr + 3) * 4, st));
   K1Params K;
   K.W = e->W; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
   K.ctl = e->ctl; K.stepinfo = e->stepinfo;
@@ -511,13 +511,15 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     S.rowflag_mc = e->symm_mc ? (uint32_t*)(e->symm_mc + e->off_rowflag[par]) : nullptr;
     S.phase = phase;
     // priority column tiles = the ones covering block column t+1 (what K1(t+1) reads)
-    S.pct0 = (int)(((t + 1) * e->m) / JB_BN);
+    // ... plus block column t itself: a swapped-in row takes its L operand from the swap buffer's
+    // column block t, so the ROWT pushes (and hence SCALE) of those tiles must be in the same phase
+    S.pct0 = (int)((t * e->m) / JB_BN);
     S.pct1 = (int)std::min<int64_t>(e->CT - 1, ((t + 2) * e->m - 1) / JB_BN);
     if (e->tc05) {  // no priority tiles: phase A = scale/broadcast/swap, phase B = all UPD tiles
       S.pct0 = 0;
       S.pct1 = -1;
     }
-    S.counter = e->counters + 2 * t + (phase == JB_PHASE_B ? 1 : 0);
+    S.counter = e->counters + 3 * t + (phase == JB_PHASE_B ? 1 : (phase == JB_PHASE_A2 ? 2 : 0));
     S.only_swapped = (e->tc05 && phase == JB_PHASE_B) ? 1 : 0;
     e->launches += 1;
     return jb_launch_step(S, e->maps[par], grid, s);
@@ -564,13 +566,14 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evA[t & 1], 0));
       JB_CHECK(launch_k1(t + 1, e->hstream));
       JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
+      JB_CHECK(launch_step(t, JB_PHASE_A2, st));  // rest of the scale/broadcast/swap (owner ranks)
       JB_CHECK(launch_step(t, JB_PHASE_B, st));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
       JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
     } else if (e->tc05) {
       // A with an EMPTY priority range = scale + broadcast + swap only; then the tcgen05 update of
       // everything, then the fp64 kernel for the swapped-in row (if any)
-      JB_CHECK(launch_step(t, JB_PHASE_A, st));
+      JB_CHECK(launch_step(t, JB_PHASE_A2, st));
       int rc5 = launch_tc05_b(t, st);
       if (rc5) return rc5;
       JB_CHECK(launch_step(t, JB_PHASE_B, st));

@@ -49,7 +49,7 @@ struct StepParams {
   uint32_t* counter;      // work-item counter of THIS launch (zeroed by the host)
   int only_swapped;       // phase B in tcgen05 mode: only the swapped-in block row stays on the fp64 path
 };
-enum { JB_PHASE_ALL = 0, JB_PHASE_A = 1, JB_PHASE_B = 2 };
+enum { JB_PHASE_ALL = 0, JB_PHASE_A = 1, JB_PHASE_B = 2, JB_PHASE_A2 = 3 };
 struct StepMaps {
   CUtensorMap tmW;     // W              box {JB_RS, JB_BK}
   CUtensorMap tmRow;   // rowbuf[par]    box {JB_RS, JB_BK}

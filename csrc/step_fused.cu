@@ -49,31 +49,39 @@ struct Plan {
 
 // Work list per phase (items are claimed IN ORDER from a global counter, so anything an item waits
 // for inside the same launch has a lower index and is already running):
-//   ALL : SCALE, ROWT, UPD over every column tile              (no look-ahead)
-//   A   : SCALE (priority column tiles first), ROWT, UPD of the priority column tiles
-//   B   : UPD of all other column tiles  (overlaps with K1(t+1) running on another stream)
+//   ALL : SCALE, ROWT, UPD over every column tile                        (no look-ahead)
+//   A   : SCALE + ROWT + UPD of the PRIORITY column tiles only (block column t+1): the minimum that
+//         K1(t+1) needs, so the pivot search of the next step can start after a ~30 us kernel
+//   A2  : SCALE + ROWT of all other column tiles (owner of the pivot row / of row t only)
+//   B   : UPD of all other column tiles; runs right behind A2 and is flag-synchronised with it tile
+//         by tile, also across GPUs, while K1(t+1) runs beside it on another stream
 __device__ __forceinline__ Plan make_plan(const StepParams& P, const JbStepInfo& si) {
   Plan pl;
   pl.npri = (P.phase == JB_PHASE_ALL || P.pct1 < P.pct0) ? 0 : (P.pct1 - P.pct0 + 1);
   pl.rtu = (P.rloc - (P.t_slot >= 0 ? 1 : 0)) * P.nsub;
+  const bool owner = (si.piv_rank == P.rank);
+  const bool has_t = (P.t_slot >= 0);
+  int cts = P.CT;  // column tiles this phase scales / installs
+  if (P.phase == JB_PHASE_A) cts = pl.npri;
+  else if (P.phase == JB_PHASE_A2) cts = P.CT - pl.npri;
   if (P.phase == JB_PHASE_B) {
     pl.nscale = 0;
     pl.nrowt = 0;
     pl.nupd = pl.rtu * (P.CT - pl.npri);
   } else {
-    pl.nscale = (si.piv_rank == P.rank) ? P.nsub * P.CT : 0;
-    pl.nrowt = (P.t_slot >= 0) ? P.CT * P.nsub : 0;
-    pl.nupd = pl.rtu * (P.phase == JB_PHASE_ALL ? P.CT : pl.npri);
+    pl.nscale = owner ? P.nsub * cts : 0;
+    pl.nrowt = has_t ? P.nsub * cts : 0;
+    pl.nupd = (P.phase == JB_PHASE_A2) ? 0 : pl.rtu * (P.phase == JB_PHASE_ALL ? P.CT : pl.npri);
   }
   pl.total = pl.nscale + pl.nrowt + pl.nupd;
   return pl;
 }
 
-// position in "priority tiles first" order -> column tile
-__device__ __forceinline__ int ct_priority_first(const StepParams& P, const Plan& pl, int pos) {
-  if (pos < pl.npri) return P.pct0 + pos;
-  const int c = pos - pl.npri;
-  return c < P.pct0 ? c : c + pl.npri;
+// position -> column tile for the SCALE / ROWT items of this phase
+__device__ __forceinline__ int ct_of_pos(const StepParams& P, const Plan& pl, int pos) {
+  if (P.phase == JB_PHASE_A) return P.pct0 + pos;
+  if (P.phase == JB_PHASE_A2) return pos < P.pct0 ? pos : pos + pl.npri;
+  return pos;
 }
 
 __device__ __forceinline__ Item decode(const StepParams& P, const JbStepInfo& si, const Plan& pl,
@@ -83,13 +91,13 @@ __device__ __forceinline__ Item decode(const StepParams& P, const JbStepInfo& si
     it.type = IT_SCALE;
     const int pos = idx / P.nsub;
     it.sub = idx - pos * P.nsub;
-    it.ct = ct_priority_first(P, pl, pos);
+    it.ct = ct_of_pos(P, pl, pos);
     it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
   } else if (idx < pl.nscale + pl.nrowt) {
     it.type = IT_ROWT;
     const int pos = (idx - pl.nscale) / P.nsub;
     it.sub = (idx - pl.nscale) - pos * P.nsub;
-    it.ct = ct_priority_first(P, pl, pos);
+    it.ct = ct_of_pos(P, pl, pos);
     it.lrow0 = P.t_slot * P.m + it.sub * JB_BM;
   } else {
     int u = idx - pl.nscale - pl.nrowt;
