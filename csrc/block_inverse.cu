@@ -68,8 +68,23 @@ __device__ void minloc_exchange(const K1Params& P, int best_slot, double best_no
   const JbMail* box = P.mail_peers[P.rank] + par * JB_MAX_RANKS;
   for (int r = 0; r < P.p; ++r) {
     const JbMail* src = box + r;
-    while (ld_acquire_sys_u32(&src->tag) != P.tag) {
-      __nanosleep(32);
+    {  // watchdog: a peer that never publishes its candidate must not hang this GPU
+      unsigned long long t0 = 0;
+      unsigned spins = 0;
+      while (ld_acquire_sys_u32(&src->tag) != P.tag) {
+        __nanosleep(32);
+        if ((++spins & 1023u) == 0) {
+          if (*(volatile int*)&P.ctl->timeout_flag) break;
+          if (P.ctl->spin_timeout_ns) {
+            const unsigned long long now = globaltimer_ns();
+            if (!t0) t0 = now;
+            else if (now - t0 > P.ctl->spin_timeout_ns) {
+              *(volatile int*)&P.ctl->timeout_flag = 1;
+              break;
+            }
+          }
+        }
+      }
     }
     JbMail cur;
     cur.norm = *(volatile const double*)&src->norm;
@@ -171,7 +186,7 @@ __global__ void __launch_bounds__(NW * 32, 1) k1_fast(const K1Params P) {
   int crank = 0;
   if constexpr (CS > 1) crank = (int)cg::this_cluster().block_rank();
   const int group = blockIdx.x / CS;
-  if (P.ctl->singular) return;
+  if (P.ctl->singular | P.ctl->timeout_flag) return;
   if (group >= P.ngroups) {
     panel_copy(P, blockIdx.x - P.ngroups * CS, gridDim.x - P.ngroups * CS);
     return;
@@ -398,7 +413,7 @@ __global__ void __launch_bounds__(K1_THREADS, 1) k1_pivot_search(const K1Params 
   if constexpr (CS > 1) crank = (int)cg::this_cluster().block_rank();
   const int group = blockIdx.x / CS;
 
-  if (P.ctl->singular) return;  // an earlier step found the matrix singular: drain
+  if (P.ctl->singular | P.ctl->timeout_flag) return;  // singular / aborted earlier: drain
 
   // ---------------------------------------------------------------- panel-copy CTAs
   if (group >= P.ngroups) {

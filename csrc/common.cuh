@@ -24,6 +24,7 @@ enum {
   JB_ERR_NOMEM = -3,      // same code as main.cpp:989
   JB_ERR_ARG = -4,
   JB_ERR_IO = -5,
+  JB_ERR_TIMEOUT = -6,  // a cross-GPU spin-wait gave up (failure detection)
 };
 
 void jb_set_error(const char* fmt, ...);
@@ -116,11 +117,35 @@ __device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v)
 __device__ __forceinline__ void fence_acq_rel_sys() {
   asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
-// spin until *p >= want (monotonic epoch counters)
-__device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t want) {
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// spin until *p >= want (monotonic epoch counters).  Failure detection (the reference has none: a
+// dead rank hangs the job): with a watchdog (abort != nullptr, timeout_ns > 0) the wait gives up
+// after timeout_ns, raises *abort so that every other wait and every later kernel drains, and
+// returns false; the host reports JB_ERR_TIMEOUT.
+__device__ __forceinline__ bool wait_flag_ge(const uint32_t* p, uint32_t want, int* abort = nullptr,
+                                             unsigned long long timeout_ns = 0) {
+  unsigned long long t0 = 0;
+  unsigned spins = 0;
   while ((int32_t)(ld_acquire_sys_u32(p) - want) < 0) {
     __nanosleep(20);
+    if (abort && ((++spins & 1023u) == 0)) {
+      if (*(volatile int*)abort) return false;
+      if (timeout_ns) {
+        const unsigned long long now = globaltimer_ns();
+        if (!t0) t0 = now;
+        else if (now - t0 > timeout_ns) {
+          *(volatile int*)abort = 1;
+          __threadfence_system();
+          return false;
+        }
+      }
+    }
   }
+  return true;
 }
 
 // ---------------------------------------------------------------- NVLS multicast (multimem)

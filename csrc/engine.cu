@@ -226,6 +226,11 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   e->off_mail = off; off += align_up(2 * JB_MAX_RANKS * sizeof(JbMail), 256);
   e->symm_bytes = align_up(off, 4096);
   e->W_peers[e->rank] = e->W;
+  {  // watchdog for cross-GPU spin-waits: default 30 s, JB_SPIN_TIMEOUT_MS=0 disables it
+    unsigned long long ns = 30ull * 1000 * 1000 * 1000;
+    if (const char* t = getenv("JB_SPIN_TIMEOUT_MS")) ns = strtoull(t, nullptr, 10) * 1000000ull;
+    cudaMemcpy(&e->ctl->spin_timeout_ns, &ns, 8, cudaMemcpyHostToDevice);
+  }
   if (getenv("JB_TIME_KERNELS")) e->profile = true;
   if (getenv("JB_NO_LOOKAHEAD")) e->lookahead = false;
   {
@@ -629,6 +634,10 @@ int jb_engine_status(JbEngine* e, void* stream) {
   JB_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
   JbCtl c;
   JB_CHECK(cudaMemcpy(&c, e->ctl, sizeof(c), cudaMemcpyDeviceToHost));
+  if (c.timeout_flag) {
+    jb_set_error("a cross-GPU wait timed out (a peer rank died or fell out of step); results are invalid");
+    return JB_ERR_TIMEOUT;
+  }
   if (c.singular) {
     jb_set_error("singular matrix (step %d)", c.singular_step);  // main.cpp:438
     return JB_ERR_SINGULAR;

@@ -39,6 +39,9 @@ struct JbCtl {
   int32_t singular_step;
   uint32_t ticket;         // K1 arrival counter (last candidate CTA performs the min-loc)
   uint32_t swap_count;     // number of block-row swaps performed so far (monotonic)
+  int32_t timeout_flag;    // a spin-wait gave up (peer dead / protocol error): results are invalid
+  int32_t pad0;
   double norm_a;           // GLOBAL ||A||_inf (the reference uses the rank-local one)
   double residual_bits;    // scratch for atomic max of |row sums|
+  unsigned long long spin_timeout_ns;  // watchdog for cross-GPU spin-waits (0 = wait forever)
 };

@@ -142,7 +142,9 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   const int warp = tid >> 5;
   const int lane = tid & 31;
 
-  if (P.ctl->singular) return;
+  if (P.ctl->singular | P.ctl->timeout_flag) return;
+  int* const abort_flag = const_cast<int*>(&P.ctl->timeout_flag);
+  const unsigned long long spin_to = P.ctl->spin_timeout_ns;
   const JbStepInfo si = P.stepinfo[P.t];
   const Plan pl = make_plan(P, si);
   if (pl.total == 0) return;
@@ -197,9 +199,9 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;  // tcgen05 mode: the rest is done there
         const int col0 = it.ct * JB_BN;
         if (kUpdOnly || it.type != IT_SCALE) {
-          wait_flag_ge(rowflag_local + it.ct, P.row_expect);  // pivot-row tile landed
+          wait_flag_ge(rowflag_local + it.ct, P.row_expect, abort_flag, spin_to);  // pivot-row tile landed
           if (it.type == IT_UPD_SWAPPED)
-            for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c * P.nsub + it.sub, P.tag);
+            for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c * P.nsub + it.sub, P.tag, abort_flag, spin_to);
           fence_proxy_async();  // remote generic-proxy writes -> my async-proxy (TMA) reads
         }
         for (int c = 0; c < KC; ++c, ++it_cnt) {
@@ -266,7 +268,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         named_bar_sync(1, MMA_WARPS * 32);
         if (tid == 0) st_release_sys_u32(P.swapflag_peers[si.piv_rank] + it.ct * P.nsub + it.sub, P.tag);
       }
-      if (lane == 0) wait_flag_ge(rowflag_local + it.ct, P.row_expect);
+      if (lane == 0) wait_flag_ge(rowflag_local + it.ct, P.row_expect, abort_flag, spin_to);
       __syncwarp();
       const double* src = rowbuf_local + roff;
       for (int r0 = rh; r0 < it.rows_valid; r0 += 8) {
@@ -296,7 +298,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         cbase = P.W + (int64_t)it.lrow0 * P.ldw;
       } else {
         if (lane == 0) {
-          wait_flag_ge(swapflag_local + it.ct * P.nsub + it.sub, P.tag);
+          wait_flag_ge(swapflag_local + it.ct * P.nsub + it.sub, P.tag, abort_flag, spin_to);
         }
         __syncwarp();
         cbase = swapbuf_local + (int64_t)(it.sub * JB_BM) * P.ldw;

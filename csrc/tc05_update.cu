@@ -198,7 +198,7 @@ k_tc05_update(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
   __shared__ __align__(16) double cs_tile[2][TC_N];  // column scales of the tile in flight (bulk-copied)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (P.ctl && P.ctl->singular) return;
+  if (P.ctl && (P.ctl->singular | P.ctl->timeout_flag)) return;
 
   // rows excluded from this kernel
   int64_t skipA0 = P.skip0, skipA1 = P.skip0 + P.skiplen, skipB0 = P.skip1, skipB1 = P.skip1 + P.skiplen1;
@@ -408,7 +408,7 @@ k_tc05_update_v2(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
   __shared__ __align__(16) double cs_tile[8][V2_N];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (P.ctl && P.ctl->singular) return;
+  if (P.ctl && (P.ctl->singular | P.ctl->timeout_flag)) return;
 
   // excluded row tiles (block row t; swapped-in row), as sorted, disjoint tile intervals
   int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
@@ -624,7 +624,7 @@ k_tc05_update_v2(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
 __global__ void __launch_bounds__(256) k_zero_cols(double* W, int64_t ldw, int64_t rows, int64_t col0,
                                                    int ncols, int64_t skip0, int64_t skiplen,
                                                    const JbCtl* ctl) {
-  if (ctl && ctl->singular) return;
+  if (ctl && (ctl->singular | ctl->timeout_flag)) return;
   for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
     if (r >= skip0 && r < skip0 + skiplen) continue;
     for (int c = threadIdx.x; c < ncols; c += blockDim.x) W[r * ldw + col0 + c] = 0.0;

@@ -20,6 +20,7 @@ extern "C" {
 #define JB_ERR_NOMEM (-3)    /* main.cpp:989 */
 #define JB_ERR_ARG (-4)
 #define JB_ERR_IO (-5)
+#define JB_ERR_TIMEOUT (-6) /* a cross-GPU wait gave up: a peer died or fell out of step */
 const char* jb_last_error(void);
 
 /* ------------------------------------------------------------------ block-cyclic layout math

@@ -22,6 +22,7 @@ JB_ERR_SINGULAR = -2
 JB_ERR_NOMEM = -3
 JB_ERR_ARG = -4
 JB_ERR_IO = -5
+JB_ERR_TIMEOUT = -6
 
 
 class JbConfig(C.Structure):

@@ -83,6 +83,25 @@ def main():
         Xo, pivo = cpu_block_jordan(A, 128, p)
         results.append({"case": "tc05", "ok": bool(piv == pivo and float((X - Xo).abs().max() / Xo.abs().max()) < 1e-8)})
     s.close()
+    # failure detection: rank 1 never joins the elimination -> the others must give up with
+    # JB_ERR_TIMEOUT instead of hanging the GPU (watchdog in the cross-GPU spin-waits)
+    os.environ["JB_SPIN_TIMEOUT_MS"] = "400"
+    s = JordanSolver(256, 64, comm=comm, device=dev, symm=mode)
+    os.environ.pop("JB_SPIN_TIMEOUT_MS")
+    s.fill_formula(1)
+    code = 0
+    if comm.rank != 1:
+        try:
+            s.invert_async()
+            s.status()
+        except _native.NativeError as exc:
+            code = exc.code
+    torch.cuda.synchronize()
+    codes = comm.allgather_obj(code)
+    if comm.rank == 0:
+        results.append({"case": "watchdog", "codes": codes,
+                        "ok": all(c == _native.JB_ERR_TIMEOUT for i, c in enumerate(codes) if i != 1)})
+    s.close()
     if comm.rank == 0:
         print("MPRESULT " + json.dumps(results), flush=True)
     comm.barrier()
