@@ -514,15 +514,16 @@ k_tc05_update_v2(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
         const uint64_t bdesc0 = umma_desc_sw128(bbase + st * V2_B_STAGE);
         const uint32_t dbase = tmem_base + tb * (TC_SMAX * V2_N);
         if (P.dbg != 3)
+        // One wide MMA per (slice s, k-step): A_s * [B_0 | ... | B_{S-1-s}] lands on the adjacent
+        // accumulators D[s .. S-1] (see k_tc05_update_v3 for the reasoning).
 #pragma unroll
-        for (int d = 0; d < S_; ++d) {
+        for (int k4 = 0; k4 < TC_K / 32; ++k4) {
 #pragma unroll
-          for (int s = 0; s <= d; ++s) {
-#pragma unroll
-            for (int k4 = 0; k4 < TC_K / 32; ++k4)
-              umma_i8(dbase + d * V2_N, adesc0 + (uint64_t)(s * (A_SLICE_BYTES / 16) + k4 * 2),
-                      bdesc0 + (uint64_t)((d - s) * (V2_B_SLICE / 16) + k4 * 2), idesc,
-                      (s > 0 || k4 > 0) ? 1u : 0u);
+          for (int s = 0; s < S_; ++s) {
+            constexpr uint32_t kIdescBase = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_M >> 4) << 24);
+            const uint32_t idesc_s = kIdescBase | ((uint32_t)(((S_ - s) * V2_N) >> 3) << 17);
+            umma_i8(dbase + s * V2_N, adesc0 + (uint64_t)(s * (A_SLICE_BYTES / 16) + k4 * 2),
+                    bdesc0 + (uint64_t)(k4 * 2), idesc_s, (s > 0 || k4 > 0) ? 1u : 0u);
           }
         }
         umma_commit(&b_free[st]);
@@ -608,6 +609,259 @@ k_tc05_update_v2(const Tc05Params P, const __grid_constant__ CUtensorMap tmA,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&t_free[tb]);
+    }
+    if (ep_tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// v3 (default for S = 8; JB_TC05_NO_V3=1 falls back to v2): A slices live in TENSOR MEMORY.  In the SS form every
+// tcgen05.mma re-reads its 4 KB A operand from shared memory, which at the small N that TMEM
+// capacity allows costs ~5x the math (profiles/README.md).  Here the epilogue threads (thread =
+// row = TMEM lane) load their rows of the S slices from L2 once per row tile and tcgen05.st them
+// into TMEM columns [0, 256); the MMAs use the TS form (A from TMEM, B from smem through a
+// 4-stage TMA ring); the 8 accumulators of one 128 x 32 tile occupy columns [256, 512).
+// ---------------------------------------------------------------------------------------------
+constexpr int V3_STAGES = 4;
+constexpr int V3_SMEM = V3_STAGES * V2_B_STAGE + 2 * V2_STG_HALF;  // 160 KB
+constexpr int V3_ACC0 = 256;                                        // first accumulator column
+
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u), "r"(0u), "r"(0u),
+      "r"(0u)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+      "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+      "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+      "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+
+template <int S_>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_tc05_update_v3(const Tc05Params P, const int8_t* __restrict__ Lq, int64_t rows_pad,
+                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmC) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t a_full, a_free, b_full[V3_STAGES], b_free[V3_STAGES], t_full, t_free;
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ __align__(16) double cs_tile[8][V2_N];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (P.ctl && (P.ctl->singular | P.ctl->timeout_flag)) return;
+
+  int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+  if (P.skiplen > 0) {
+    a0 = (int)(P.skip0 / TC_M);
+    a1 = (int)((P.skip0 + P.skiplen) / TC_M);
+  }
+  if (P.stepinfo) {
+    const JbStepInfo si = P.stepinfo[P.t];
+    if (si.do_swap && si.piv_rank == P.rank) {
+      b0 = (int)(((int64_t)si.piv_slot * P.m) / TC_M);
+      b1 = (int)(((int64_t)(si.piv_slot + 1) * P.m) / TC_M);
+    }
+  }
+  if (b1 > b0 && (a1 <= a0 || b0 < a0)) {
+    int t0 = a0, t1 = a1;
+    a0 = b0; a1 = b1; b0 = t0; b1 = t1;
+  }
+  const int vrt_count = P.rt_count - (a1 - a0) - (b1 - b0);
+  const int64_t total = (int64_t)vrt_count * P.ct_count;
+  const int64_t lo = total * blockIdx.x / gridDim.x, hi = total * (blockIdx.x + 1) / gridDim.x;
+
+  unsigned char* sB = smem;
+  unsigned char* sStg = smem + V3_STAGES * V2_B_STAGE;
+
+  if (tid == 0) {
+    mbar_init(&a_full, 4);   // one arrive per epilogue warp after its tcgen05.st are done
+    mbar_init(&a_free, 1);
+    for (int i = 0; i < V3_STAGES; ++i) {
+      mbar_init(&b_full[i], 1);
+      mbar_init(&b_free[i], 1);
+    }
+    mbar_init(&t_full, 1);
+    mbar_init(&t_free, 4);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+        smem_u32(&tmem_base_smem)), "r"(512u));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer (B only)
+    if (lane == 0 && lo < hi) {
+      tma_prefetch_desc(&tmB);
+      uint32_t nb = 0;
+      for (int64_t idx = lo; idx < hi; ++idx, ++nb) {
+        const int ct = (int)(idx % P.ct_count);
+        const int st = nb % V3_STAGES;
+        mbar_wait(&b_free[st], ((nb / V3_STAGES) & 1) ^ 1);
+        mbar_expect_tx(&b_full[st], (uint32_t)S_ * V2_B_SLICE + (uint32_t)(V2_N * 8));
+        for (int s = 0; s < S_; ++s)
+          tma_load_3d(sB + (size_t)st * V2_B_STAGE + (size_t)s * V2_B_SLICE, &tmB, 0, ct * V2_N, s,
+                      &b_full[st]);
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+            ::"r"(smem_u32(&cs_tile[nb & 7][0])), "l"(P.cscale + (int64_t)ct * V2_N),
+            "r"((uint32_t)(V2_N * 8)), "r"(smem_u32(&b_full[st]))
+            : "memory");
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer (TS form)
+    if (lane == 0 && lo < hi) {
+      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(V2_N >> 3) << 17) |
+                             ((uint32_t)(TC_M >> 4) << 24);
+      const uint32_t bbase = smem_u32(sB);
+      int cur_rt = -1;
+      uint32_t na = 0, nb = 0;
+      for (int64_t idx = lo; idx < hi; ++idx, ++nb) {
+        const int rt = map_valid_rt((int)(idx / P.ct_count), a0, a1, b0, b1);
+        if (rt != cur_rt) {
+          mbar_wait(&a_full, na & 1);  // the epilogue warps have stored this row tile's A slices
+          ++na;
+          cur_rt = rt;
+        }
+        const int st = nb % V3_STAGES;
+        mbar_wait(&t_free, (nb & 1) ^ 1);
+        mbar_wait(&b_full[st], (nb / V3_STAGES) & 1);
+        tc_fence_after();
+        const uint64_t bdesc0 = umma_desc_sw128(bbase + st * V2_B_STAGE);
+        const uint32_t dbase = tmem_base + V3_ACC0;
+        // The cost of a tcgen05.mma is dominated by delivering its 128 x 32-byte A operand (~64-80
+        // cycles, independent of N), so N must be large.  The accumulators D[d] of consecutive
+        // diagonals are adjacent TMEM column blocks and the B slices are adjacent 32-row blocks of
+        // one K-major smem matrix, hence  A_s * [B_0 | B_1 | ... | B_{S-1-s}]  is ONE MMA with
+        // N = 32 (S - s) that lands exactly on D[s .. S-1]:  4 S instructions per tile instead of
+        // 2 S (S + 1).
+#pragma unroll
+        for (int k4 = 0; k4 < TC_K / 32; ++k4) {
+#pragma unroll
+          for (int s = 0; s < S_; ++s) {
+            constexpr uint32_t kIdescBase = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_M >> 4) << 24);
+            const uint32_t idesc_s = kIdescBase | ((uint32_t)(((S_ - s) * V2_N) >> 3) << 17);
+            umma_i8_ts(dbase + s * V2_N, tmem_base + s * 32 + k4 * 8, bdesc0 + (uint64_t)(k4 * 2), idesc_s,
+                       (s > 0 || k4 > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&b_free[st]);
+        umma_commit(&t_full);
+        const bool last_of_rt =
+            (idx + 1 >= hi) || map_valid_rt((int)((idx + 1) / P.ct_count), a0, a1, b0, b1) != rt;
+        if (last_of_rt) umma_commit(&a_free);
+      }
+    }
+  } else {
+    // ===================================================================== epilogue warps 2..5
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const int ep_tid = tid - 64;
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    int cur_rt = -1;
+    uint32_t na = 0, nb = 0;
+    double rs7 = 0.0;
+    for (int64_t idx = lo; idx < hi; ++idx, ++nb) {
+      const int vrt = (int)(idx / P.ct_count), ct = (int)(idx % P.ct_count);
+      const int rt = map_valid_rt(vrt, a0, a1, b0, b1);
+      if (rt != cur_rt) {
+        // (re)load the A slices of this row tile into TMEM: thread = row = TMEM lane
+        mbar_wait(&a_free, (na & 1) ^ 1);  // MMAs reading the previous A have retired
+        tc_fence_after();
+        const int64_t r = (int64_t)rt * TC_M + row_in_tile;
+#pragma unroll 1
+        for (int s = 0; s < S_; ++s) {
+          const uint4* src = reinterpret_cast<const uint4*>(Lq + ((int64_t)s * rows_pad + r) * TC_K);
+          uint32_t v[32];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint4 x = src[i];
+            v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+          }
+          tmem_st32(tmem_base + lane_base + (uint32_t)(s * 32), v);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_full);
+        rs7 = P.rscale[r] * 0.0078125;
+        ++na;
+        cur_rt = rt;
+      }
+      mbar_wait(&t_full, nb & 1);
+      tc_fence_after();
+      const double* cs = cs_tile[nb & 7];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        unsigned char* stg = sStg + h * V2_STG_HALF;
+        if (ep_tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        named_bar_sync(2, 128);
+#pragma unroll
+        for (int c8 = 0; c8 < 16; c8 += 8) {
+          int32_t v[TC_SMAX][8];
+#pragma unroll
+          for (int d = 0; d < TC_SMAX; ++d) {
+            if (d < S_) {
+              tmem_ld8(tmem_base + lane_base + (uint32_t)(V3_ACC0 + d * V2_N + h * 16 + c8), v[d]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[d][i] = 0;
+            }
+          }
+          tmem_wait_ld();
+          if (h == 1 && c8 == 8) {  // last TMEM read of this tile: the MMA of the next tile may start
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&t_free);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            double o0 = 0.0, o1 = 0.0;
+#pragma unroll
+            for (int j = TC_SMAX / 2 - 1; j >= 0; --j) {
+              const int w0 = v[2 * j][i] * 128 + v[2 * j + 1][i];
+              const int w1 = v[2 * j][i + 1] * 128 + v[2 * j + 1][i + 1];
+              o0 = fma(o0, 6.103515625e-05, i32_to_f64(w0));
+              o1 = fma(o1, 6.103515625e-05, i32_to_f64(w1));
+            }
+            o0 *= rs7 * cs[h * 16 + c8 + i];
+            o1 *= rs7 * cs[h * 16 + c8 + i + 1];
+            const int chunk = ((c8 + i) >> 1) ^ (row_in_tile & 7);  // SWIZZLE_128B
+            *reinterpret_cast<double2*>(stg + row_in_tile * 128 + chunk * 16) = make_double2(o0, o1);
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        named_bar_sync(3, 128);
+        if (ep_tid == 0) {
+          asm volatile(
+              "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];"
+              ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(ct * V2_N + h * 16), "r"(rt * TC_M),
+              "r"(smem_u32(stg))
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
     }
     if (ep_tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
@@ -747,6 +1001,7 @@ int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v3<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, V3_SMEM));
     configured[dev % JB_MAX_RANKS] = true;
   }
   if (P.rt_count == 0 || a.cols == 0) return JB_OK;
@@ -764,7 +1019,9 @@ int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
                                        a.skiplen, a.ctl);
       JB_CHECK(cudaGetLastError());
     }
-    if (a.S == 8) k_tc05_update_v2<8><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
+    static const bool use_v3 = getenv("JB_TC05_NO_V3") == nullptr;  // A-in-TMEM kernel (default for S = 8)
+    if (a.S == 8 && use_v3) k_tc05_update_v3<8><<<a.grid, TC_THREADS, V3_SMEM, st>>>(P, a.Lq, a.rows_pad, tmB, tmC);
+    else if (a.S == 8) k_tc05_update_v2<8><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
     else if (a.S == 7) k_tc05_update_v2<7><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
     else if (a.S == 6) k_tc05_update_v2<6><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
     else {
