@@ -132,3 +132,16 @@ def test_extended_selectors():
 def test_format_corner_is_printf_exact():
     t = torch.tensor([[0.005, -0.004, 1234.567], [1e-9, -1e-9, 2.0]], dtype=torch.float64)
     assert jio.format_corner(t) == "0.01\t-0.00\t1234.57\t\n0.00\t-0.00\t2.00\t\n".replace("0.01", "%.2f" % 0.005)
+
+
+def test_reference_bench_arm_line(reference):
+    """bench.py --impl reference: unmodified reference through its own CLI, one JSON line."""
+    import json
+
+    env = dict(os.environ, JB_REF_BUDGET_S="30")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+                        "--n", "600", "--m", "60"], capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and d["metric"] == "fp64_inverse_gflops" and d["n_gpus"] == 2
+    assert d["config"]["n"] == 600 and d["value"] > 0 and d["gpu_launches"] == 0
