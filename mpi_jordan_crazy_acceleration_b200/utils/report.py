@@ -7,8 +7,6 @@ Error lines: ``usage:%s n m [<file>]`` (rc 1), ``cannot open %s`` / ``cannot rea
 """
 from __future__ import annotations
 
-import ctypes as C
-
 
 def c_format(fmt: str, value: float) -> str:
     """printf-exact formatting of one double (Python's % operator matches C for %e / %.2f)."""
@@ -30,5 +28,3 @@ def report_time(seconds: float) -> str:
 def report_residual(res: float) -> str:
     return "residual: %e\n" % res
 
-
-_ = C
