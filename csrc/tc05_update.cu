@@ -1002,6 +1002,8 @@ int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v2<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, V2_SMEM));
     JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v3<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, V3_SMEM));
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v3<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, V3_SMEM));
+    JB_CHECK(cudaFuncSetAttribute(k_tc05_update_v3<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, V3_SMEM));
     configured[dev % JB_MAX_RANKS] = true;
   }
   if (P.rt_count == 0 || a.cols == 0) return JB_OK;
@@ -1019,8 +1021,13 @@ int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
                                        a.skiplen, a.ctl);
       JB_CHECK(cudaGetLastError());
     }
-    static const bool use_v3 = getenv("JB_TC05_NO_V3") == nullptr;  // A-in-TMEM kernel (default for S = 8)
+    static const bool use_v3 = getenv("JB_TC05_NO_V3") == nullptr;  // A-in-TMEM kernel (default)
+    // S = 8 is the validated default; 7 / 6 slices (JB_TC05_SLICES) trade accuracy for speed and use the
+    // v2 kernel unless JB_TC05_V3_ALL=1 (same code, other loop bounds; not measured this round)
+    static const bool v3_all = getenv("JB_TC05_V3_ALL") != nullptr;
     if (a.S == 8 && use_v3) k_tc05_update_v3<8><<<a.grid, TC_THREADS, V3_SMEM, st>>>(P, a.Lq, a.rows_pad, tmB, tmC);
+    else if (a.S == 7 && use_v3 && v3_all) k_tc05_update_v3<7><<<a.grid, TC_THREADS, V3_SMEM, st>>>(P, a.Lq, a.rows_pad, tmB, tmC);
+    else if (a.S == 6 && use_v3 && v3_all) k_tc05_update_v3<6><<<a.grid, TC_THREADS, V3_SMEM, st>>>(P, a.Lq, a.rows_pad, tmB, tmC);
     else if (a.S == 8) k_tc05_update_v2<8><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
     else if (a.S == 7) k_tc05_update_v2<7><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
     else if (a.S == 6) k_tc05_update_v2<6><<<a.grid, TC_THREADS, V2_SMEM, st>>>(P, tmA, tmB, tmC);
