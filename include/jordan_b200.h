@@ -60,6 +60,12 @@ int jb_cpu_inverse_block(double* a, double* b, double norm, int64_t n);
 int jb_cpu_minloc_fold(const double* norms, const int32_t* nonsing, int64_t p);
 double jb_cpu_residual(const double* a, const double* x, int64_t n);
 
+/* Work list of the fused step kernel for one phase (CPU-side view of csrc/step_plan.h, used by the
+ * scheduling-invariant tests).  out[4*i..] = {type, column tile, first local row, rows}. */
+int64_t jb_plan_enumerate(int32_t m, int32_t p, int32_t rank, int32_t rloc, int64_t ldw, int32_t t,
+                          int32_t piv_rank, int32_t piv_slot, int32_t do_swap, int32_t phase,
+                          int32_t pct0, int32_t pct1, int32_t* out, int64_t cap);
+
 /* ------------------------------------------------------------------ GPU engine (libjordan_b200) */
 typedef struct JbEngine JbEngine;
 

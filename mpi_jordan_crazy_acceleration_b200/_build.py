@@ -22,9 +22,10 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("CXX", "g++")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v", *ARCH]
-CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-Wall"]
+CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-Wall", "-I" + os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"]
 
-HOST_SRCS = ["csrc/host/layout.cpp", "csrc/host/io_text.cpp", "csrc/host/cpu_oracle.cpp"]
+HOST_SRCS = ["csrc/host/layout.cpp", "csrc/host/io_text.cpp", "csrc/host/cpu_oracle.cpp", "csrc/host/plan_enum.cpp"]
+CUDA_INC = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
 CUDA_SRCS = [
     "csrc/block_inverse.cu",
     "csrc/step_fused.cu",
@@ -32,7 +33,7 @@ CUDA_SRCS = [
     "csrc/dist_gemm.cu",
     "csrc/engine.cu",
 ]
-CUDA_HDRS = ["csrc/common.cuh", "csrc/kernels.h", "csrc/kernels_formula.h", "csrc/engine_types.h",
+CUDA_HDRS = ["csrc/common.cuh", "csrc/kernels.h", "csrc/kernels_formula.h", "csrc/engine_types.h", "csrc/step_plan.h",
              "include/jordan_b200.h"]
 
 
@@ -56,7 +57,8 @@ def _run(cmd: list[str], log: Path | None = None) -> None:
 def build_host(force: bool = False) -> Path:
     LIBDIR.mkdir(parents=True, exist_ok=True)
     out = LIBDIR / "libjordan_host.so"
-    deps = [ROOT / s for s in HOST_SRCS] + [ROOT / "include/jordan_b200.h", ROOT / "csrc/kernels_formula.h"]
+    deps = [ROOT / s for s in HOST_SRCS] + [ROOT / "include/jordan_b200.h", ROOT / "csrc/kernels_formula.h",
+                                            ROOT / "csrc/step_plan.h", ROOT / "csrc/kernels.h"]
     if force or _newer(out, deps):
         _run([CXX, *CXX_FLAGS, "-shared", "-o", str(out), *HOST_SRCS])
     return out
