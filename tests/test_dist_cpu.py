@@ -81,3 +81,35 @@ def test_eager_gloo_world(world, tmp_path):
     assert torch.allclose(torch.tensor(f["X"], dtype=torch.float64), Xo, atol=1e-9)
     assert torch.allclose(torch.tensor(f["corner"], dtype=torch.float64), Xo[:10, :10], atol=1e-9)
     assert f["codes"] == [-1] * world          # every rank agreed on "cannot open"
+
+
+def test_cli_under_torchrun_gloo_matches_single_process(tmp_path):
+    """The CLI as an SPMD program (2 ranks, gloo): rank 0 prints the reference's report, file input is
+    scattered block row by block row, and the numbers match the single-process run."""
+    torch.manual_seed(3)
+    n, m = 48, 6
+    A = formula_rows(1, n, torch.arange(n)) + 0.25 * torch.eye(n, dtype=torch.float64)
+    path = tmp_path / "a.txt"
+    jio.write_matrix(str(path), A)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29741", "-m", "mpi_jordan_crazy_acceleration_b200.cli", str(n), str(m),
+           str(path), "--backend", "eager"]
+    env = dict(os.environ, OMP_NUM_THREADS="1", PYTHONPATH=ROOT)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip() != "" or True]
+    assert lines[0] == "A" and sum(ln.startswith("glob_time:") for ln in lines) == 1   # only rank 0 prints
+    res = float([ln for ln in lines if ln.startswith("residual:")][0].split()[1])
+    assert res < 1e-10
+    import io as _io
+
+    from mpi_jordan_crazy_acceleration_b200 import cli
+
+    buf = _io.StringIO()
+    assert cli.main([str(n), str(m), str(path), "--backend", "eager"], out=buf) == 0
+    one = [ln for ln in buf.getvalue().splitlines() if "\t" in ln]
+    two = [ln for ln in lines if "\t" in ln]
+    assert len(one) == len(two) == 20
+    a1 = torch.tensor([[float(v) for v in ln.split("\t") if v] for ln in one])
+    a2 = torch.tensor([[float(v) for v in ln.split("\t") if v] for ln in two])
+    assert torch.allclose(a1, a2, atol=0.011)
