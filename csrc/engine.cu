@@ -94,7 +94,9 @@ struct JbEngine {
   JbStepInfo* stepinfo = nullptr;
   double *Xp = nullptr, *rowsum = nullptr, *scratch_max = nullptr, *Rslab = nullptr;
   // symmetric region
-  size_t off_rowbuf[2], off_swapbuf, off_rowflag[2], off_swapflag, off_mail, symm_bytes;
+  size_t off_rowbuf[2], off_swapbuf[2], off_rowflag[2], off_swapflag[2], off_mail, symm_bytes;
+  uint32_t* prowflag = nullptr;  // [CT][nsub] local flags of the pivot-row look-ahead (phase B2)
+  double b1_frac = -1.0;         // share of the non-priority column tiles given to phase B1 (<0: auto)
   unsigned char* symm_peers[JB_MAX_RANKS] = {nullptr};
   unsigned char* symm_mc = nullptr;
   bool own_symm = false, symm_ready = false;
@@ -109,7 +111,11 @@ struct JbEngine {
   // optional per-kernel timing (JB_TIME_KERNELS=1 or jb_engine_set_profiling)
   bool profile = false;
   std::vector<cudaEvent_t> ev;
-  double prof_k1_ms = 0, prof_step_ms = 0, prof_tail_ms = 0, prof_wait_ms = 0;
+  // per-step segments summed over the inversion.  look-ahead: [0] phase A, [1] phase B1 (K1(t+1)
+  // beside it), [2] main stream still waiting for K1(t+1), [3] phase B2.  serial / tcgen05: [0] step
+  // kernel (tcgen05: scale/broadcast/swap), [1] tcgen05 update, [2] K1(t+1), [3] -
+  double prof_ms[4] = {0, 0, 0, 0};
+  double prof_tail_ms = 0;
 };
 
 namespace {
@@ -125,7 +131,7 @@ int build_maps(JbEngine* e) {
     if ((rc = make_map(&M.tmL, e->Lbuf[par], e->Kp, e->rows_loc, e->Kp, JB_LS, JB_BM))) return rc;
     if ((rc = make_map(&M.tmInv, e->invbuf, e->Kp, (uint64_t)e->rloc * e->Kp, e->Kp, JB_LS, JB_BM)))
       return rc;
-    if ((rc = make_map(&M.tmSwap, loc + e->off_swapbuf, e->ldw, e->Kp, e->ldw, JB_LS, JB_BM)))
+    if ((rc = make_map(&M.tmSwap, loc + e->off_swapbuf[par], e->ldw, e->Kp, e->ldw, JB_LS, JB_BM)))
       return rc;
   }
   e->maps_ready = true;
@@ -174,7 +180,8 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   if (r == cudaSuccess) r = dmalloc((void**)&e->W, rl * e->ldw * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[0], (rl + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[1], (rl + JB_BM) * e->Kp * 8);
-  if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(3 * e->Nr + 3) * 4);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(4 * e->Nr + 4) * 4);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->prowflag, (size_t)e->CT * e->nsub * 4);
   if (r == cudaSuccess)
     r = dmalloc((void**)&e->invbuf, ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->normbuf, (size_t)std::max(e->rloc, 1) * 8);
@@ -218,19 +225,31 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   const size_t rb = align_up((size_t)e->Kp * e->ldw * 8, 256);
   e->off_rowbuf[0] = off; off += rb;
   e->off_rowbuf[1] = off; off += rb;
-  e->off_swapbuf = off; off += rb;
+  // swap buffer and its flags are double-buffered by step parity like the pivot-row buffer: with
+  // look-ahead the ranks drift by up to one phase, so ROWT(t+1) may push while a slower pivot owner
+  // still reads what ROWT(t) pushed
+  e->off_swapbuf[0] = off; off += rb;
+  e->off_swapbuf[1] = off; off += rb;
   const size_t fb = align_up((size_t)e->CT * 4, 256);
   e->off_rowflag[0] = off; off += fb;
   e->off_rowflag[1] = off; off += fb;
-  e->off_swapflag = off; off += align_up((size_t)e->CT * e->nsub * 4, 256);  // one flag per 64-row chunk
+  const size_t sfb = align_up((size_t)e->CT * e->nsub * 4, 256);  // one flag per 64-row chunk
+  e->off_swapflag[0] = off; off += sfb;
+  e->off_swapflag[1] = off; off += sfb;
   e->off_mail = off; off += align_up(2 * JB_MAX_RANKS * sizeof(JbMail), 256);
   e->symm_bytes = align_up(off, 4096);
   e->W_peers[e->rank] = e->W;
   {  // watchdog for cross-GPU spin-waits: default 30 s, JB_SPIN_TIMEOUT_MS=0 disables it
     unsigned long long ns = 30ull * 1000 * 1000 * 1000;
     if (const char* t = getenv("JB_SPIN_TIMEOUT_MS")) ns = strtoull(t, nullptr, 10) * 1000000ull;
-    cudaMemcpy(&e->ctl->spin_timeout_ns, &ns, 8, cudaMemcpyHostToDevice);
+    if (cudaMemcpy(&e->ctl->spin_timeout_ns, &ns, 8, cudaMemcpyHostToDevice) != cudaSuccess) {
+      jb_set_error("jb_engine_create: cannot initialise the control block (%s)",
+                   cudaGetErrorString(cudaGetLastError()));
+      jb_engine_destroy(e);
+      return JB_ERR_CUDA;
+    }
   }
+  if (const char* f = getenv("JB_B1_FRAC")) e->b1_frac = std::max(0.0, std::min(1.0, atof(f)));
   if (getenv("JB_TIME_KERNELS")) e->profile = true;
   if (getenv("JB_NO_LOOKAHEAD")) e->lookahead = false;
   {
@@ -266,6 +285,7 @@ void jb_engine_destroy(JbEngine* e) {
     if (e->evK[i]) cudaEventDestroy(e->evK[i]);
   }
   cudaFree(e->counters);
+  cudaFree(e->prowflag);
   for (int i = 0; i < 2; ++i) {
     for (int kb = 0; kb < 2; ++kb) { cudaFree(e->Lq[i][kb]); cudaFree(e->rscale[i][kb]); }
     cudaFree(e->Rq[i]); cudaFree(e->cscale[i]);
@@ -358,6 +378,7 @@ int jb_engine_reset_sync(JbEngine* e) {
   unsigned char* loc = e->symm_peers[e->rank];
   if (loc) JB_CHECK(cudaMemset(loc + e->off_rowflag[0], 0, e->symm_bytes - e->off_rowflag[0]));
   JB_CHECK(cudaMemset(e->ctl, 0, offsetof(JbCtl, norm_a)));
+  JB_CHECK(cudaMemset(e->prowflag, 0, (size_t)e->CT * e->nsub * 4));
   JB_CHECK(cudaDeviceSynchronize());
   e->gstep = 0;
   return JB_OK;
@@ -452,7 +473,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   JB_CHECK(cudaMemsetAsync(e->ctl, 0, offsetof(JbCtl, norm_a), st));
 
-  JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(3 * e->Nr + 3) * 4, st));
+  JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(4 * e->Nr + 4) * 4, st));
   K1Params K;
   K.W = e->W; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
   K.ctl = e->ctl; K.stepinfo = e->stepinfo;
@@ -461,23 +482,30 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   K.ldw = e->ldw; K.m = e->m; K.Kp = e->Kp; K.p = e->p; K.rank = e->rank; K.rloc = e->rloc;
 
   StepParams S;
+  memset(&S, 0, sizeof(S));
   S.W = e->W; S.invbuf = e->invbuf; S.stepinfo = e->stepinfo; S.ctl = e->ctl;
   S.ldw = e->ldw; S.m = e->m; S.Kp = e->Kp; S.p = e->p; S.rank = e->rank;
-  S.rloc = e->rloc; S.nsub = e->nsub; S.CT = e->CT;
-  for (int r = 0; r < JB_MAX_RANKS; ++r) {
-    S.swapbuf_peers[r] = r < e->p ? (double*)(e->symm_peers[r] + e->off_swapbuf) : nullptr;
-    S.swapflag_peers[r] = r < e->p ? (uint32_t*)(e->symm_peers[r] + e->off_swapflag) : nullptr;
-  }
+  S.rloc = e->rloc; S.nsub = e->nsub; S.CT = e->CT; S.prowflag = e->prowflag;
   const int grid = 2 * e->sm_count;
   const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
-  if (e->profile && e->ev.size() < (size_t)(3 * e->Nr + 2)) {
+  const size_t nev = (size_t)(4 * e->Nr + 2);
+  if (e->profile && e->ev.size() < nev) {
     size_t old = e->ev.size();
-    e->ev.resize((size_t)(3 * e->Nr + 2));
+    e->ev.resize(nev);
     for (size_t i = old; i < e->ev.size(); ++i) JB_CHECK(cudaEventCreate(&e->ev[i]));
   }
   const uint32_t g0 = e->gstep;
   e->gstep += (uint32_t)e->Nr;
   const bool la = e->lookahead && e->Nr > 1 && !e->tc05;
+  // Share of the non-priority column tiles that phase B1 updates while K1(t+1) runs beside it.  B1
+  // should last about as long as K1 (~1.5 us per elimination column, 2.6 us with a 4-CTA cluster)
+  // plus the skew between ranks; everything after it (phase B2) already knows the next pivot.
+  double frac = e->b1_frac;
+  if (frac < 0) {
+    const double k1_us = (e->m > 128 ? 2.6 : 1.5) * e->m + 20.0;
+    const double b_us = 2.0 * (double)e->rows_loc * (double)e->ldw * e->m / 30e6;
+    frac = std::max(0.25, std::min(0.85, 1.4 * k1_us / std::max(b_us, 1.0)));
+  }
 
   // K1 of step t: candidates are the local block rows with global index >= t (main.cpp:1028)
   auto launch_k1 = [&](int64_t t, cudaStream_t s) -> cudaError_t {
@@ -501,30 +529,56 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     }
     return ce;
   };
-  auto launch_step = [&](int64_t t, int phase, cudaStream_t s) -> cudaError_t {
+  // `wide` = every column tile is a priority tile (last step of the look-ahead schedule: phase A
+  // then is ROWT + UPD of the whole row, nothing is left for B1 / B2)
+  auto launch_step = [&](int64_t t, int phase, cudaStream_t s, bool wide = false) -> cudaError_t {
     const uint32_t g = g0 + (uint32_t)t;
     const int par = g & 1;
     S.t = (int)t;
     S.t_slot = (t % e->p == e->rank) ? (int)(t / e->p) : -1;
     S.row_expect = ((g >> 1) + 1) * (uint32_t)e->nsub;
     S.tag = g + 1;
+    // SCALE items of phase B2 produce the pivot row of step t + 1 (other buffer parity)
+    S.sc_t = (phase == JB_PHASE_B2) ? (int)t + 1 : (int)t;
+    S.has_next = (phase == JB_PHASE_B2 && t + 1 < e->Nr) ? 1 : 0;
+    const int spar = (phase == JB_PHASE_B2) ? (par ^ 1) : par;
     for (int r = 0; r < JB_MAX_RANKS; ++r) {
-      S.rowbuf_peers[r] = r < e->p ? (double*)(e->symm_peers[r] + e->off_rowbuf[par]) : nullptr;
-      S.rowflag_peers[r] = r < e->p ? (uint32_t*)(e->symm_peers[r] + e->off_rowflag[par]) : nullptr;
+      unsigned char* base = r < e->p ? e->symm_peers[r] : nullptr;
+      S.rowbuf_peers[r] = base ? (double*)(base + e->off_rowbuf[par]) : nullptr;
+      S.rowflag_peers[r] = base ? (uint32_t*)(base + e->off_rowflag[par]) : nullptr;
+      S.swapbuf_peers[r] = base ? (double*)(base + e->off_swapbuf[par]) : nullptr;
+      S.swapflag_peers[r] = base ? (uint32_t*)(base + e->off_swapflag[par]) : nullptr;
+      S.sc_rowbuf_peers[r] = base ? (double*)(base + e->off_rowbuf[spar]) : nullptr;
+      S.sc_rowflag_peers[r] = base ? (uint32_t*)(base + e->off_rowflag[spar]) : nullptr;
     }
     S.rowbuf_mc = e->symm_mc ? (double*)(e->symm_mc + e->off_rowbuf[par]) : nullptr;
     S.rowflag_mc = e->symm_mc ? (uint32_t*)(e->symm_mc + e->off_rowflag[par]) : nullptr;
+    S.sc_rowbuf_mc = e->symm_mc ? (double*)(e->symm_mc + e->off_rowbuf[spar]) : nullptr;
+    S.sc_rowflag_mc = e->symm_mc ? (uint32_t*)(e->symm_mc + e->off_rowflag[spar]) : nullptr;
     S.phase = phase;
     // priority column tiles = the ones covering block column t+1 (what K1(t+1) reads)
     // ... plus block column t itself: a swapped-in row takes its L operand from the swap buffer's
-    // column block t, so the ROWT pushes (and hence SCALE) of those tiles must be in the same phase
+    // column block t, so the ROWT pushes of those tiles must be in the same phase
     S.pct0 = (int)((t * e->m) / JB_BN);
     S.pct1 = (int)std::min<int64_t>(e->CT - 1, ((t + 2) * e->m - 1) / JB_BN);
-    if (e->tc05) {  // no priority tiles: phase A = scale/broadcast/swap, phase B = all UPD tiles
+    if (wide) {
+      S.pct0 = 0;
+      S.pct1 = e->CT - 1;
+    }
+    if (e->tc05) {  // no priority tiles: phase A2 = scale/broadcast/swap, phase B = swapped-in row
       S.pct0 = 0;
       S.pct1 = -1;
     }
-    S.counter = e->counters + 3 * t + (phase == JB_PHASE_B ? 1 : (phase == JB_PHASE_A2 ? 2 : 0));
+    const int nnp = e->CT - (S.pct1 >= S.pct0 ? S.pct1 - S.pct0 + 1 : 0);
+    S.nb1 = std::min(nnp, (int)(frac * nnp + 0.999));
+    int cslot = 0;
+    switch (phase) {
+      case JB_PHASE_B: case JB_PHASE_B1: cslot = 1; break;
+      case JB_PHASE_A2: case JB_PHASE_B2: cslot = 2; break;
+      case JB_PHASE_S: cslot = 3; break;
+      default: cslot = 0;
+    }
+    S.counter = e->counters + 4 * t + cslot;
     S.only_swapped = (e->tc05 && phase == JB_PHASE_B) ? 1 : 0;
     e->launches += 1;
     return jb_launch_step(S, e->maps[par], grid, s);
@@ -560,56 +614,64 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   };
 
   JB_CHECK(launch_k1(0, st));
+  if (la) JB_CHECK(launch_step(0, JB_PHASE_S, st));  // pivot row of step 0: scale + broadcast
   for (int64_t t = 0; t < e->Nr; ++t) {
-    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t], st));
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t], st));
     if (la && t + 1 < e->Nr) {
-      // step_A(t): scale + broadcast, row swap, and the update of block column t+1
+      // A(t): row swap / install + update of block columns t, t+1 (their pivot-row tiles were
+      // broadcast during step t-1)
       JB_CHECK(launch_step(t, JB_PHASE_A, st));
       JB_CHECK(cudaEventRecord(e->evA[t & 1], st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));
-      // K1(t+1) on the high-priority stream, enqueued BEFORE step_B(t) so its CTAs get SMs first
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
+      // K1(t+1) on the high-priority stream, enqueued BEFORE B1(t) so its CTAs get SMs first
       JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evA[t & 1], 0));
       JB_CHECK(launch_k1(t + 1, e->hstream));
       JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
-      JB_CHECK(launch_step(t, JB_PHASE_A2, st));  // rest of the scale/broadcast/swap (owner ranks)
-      JB_CHECK(launch_step(t, JB_PHASE_B, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
+      JB_CHECK(launch_step(t, JB_PHASE_B1, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
       JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
+      // B2(t): knows pivot(t+1): its owner finishes that row first, scales it and broadcasts it
+      // for step t+1 while everybody is still busy with the bulk of step t
+      JB_CHECK(launch_step(t, JB_PHASE_B2, st));
+    } else if (la) {
+      JB_CHECK(launch_step(t, JB_PHASE_A, st, /*wide=*/true));  // last step: nothing to look ahead to
+      if (e->profile)
+        for (int k = 1; k <= 3; ++k) JB_CHECK(cudaEventRecord(e->ev[4 * t + k], st));
     } else if (e->tc05) {
-      // A with an EMPTY priority range = scale + broadcast + swap only; then the tcgen05 update of
+      // A2 with an EMPTY priority range = scale + broadcast + swap only; then the tcgen05 update of
       // everything, then the fp64 kernel for the swapped-in row (if any)
       JB_CHECK(launch_step(t, JB_PHASE_A2, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
       int rc5 = launch_tc05_b(t, st);
       if (rc5) return rc5;
       JB_CHECK(launch_step(t, JB_PHASE_B, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
     } else {
       JB_CHECK(launch_step(t, JB_PHASE_ALL, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * t + 2], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
     }
   }
-  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[3 * e->Nr], st));
+  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * e->Nr], st));
   JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
   e->launches += (e->rows_loc > 0);
   if (e->profile) {
-    JB_CHECK(cudaEventRecord(e->ev[3 * e->Nr + 1], st));
+    JB_CHECK(cudaEventRecord(e->ev[4 * e->Nr + 1], st));
     JB_CHECK(cudaStreamSynchronize(st));
-    e->prof_k1_ms = e->prof_step_ms = e->prof_wait_ms = 0;
-    for (int64_t t = 0; t < e->Nr; ++t) {
-      float a = 0, b = 0, c = 0;
-      JB_CHECK(cudaEventElapsedTime(&a, e->ev[3 * t], e->ev[3 * t + 1]));
-      JB_CHECK(cudaEventElapsedTime(&b, e->ev[3 * t + 1], e->ev[3 * t + 2]));
-      JB_CHECK(cudaEventElapsedTime(&c, e->ev[3 * t + 2], e->ev[3 * t + 3]));
-      e->prof_k1_ms += a;    // look-ahead: step_A(t); serial: the fused step kernel
-      e->prof_step_ms += b;  // look-ahead: step_B(t); serial: K1(t+1)
-      e->prof_wait_ms += c;  // look-ahead: time the main stream then still waits for K1(t+1)
-    }
+    for (int k = 0; k < 4; ++k) e->prof_ms[k] = 0;
+    for (int64_t t = 0; t < e->Nr; ++t)
+      for (int k = 0; k < 4; ++k) {
+        float x = 0;
+        JB_CHECK(cudaEventElapsedTime(&x, e->ev[4 * t + k], e->ev[4 * t + k + 1]));
+        e->prof_ms[k] += x;
+      }
     float c = 0;
-    JB_CHECK(cudaEventElapsedTime(&c, e->ev[3 * e->Nr], e->ev[3 * e->Nr + 1]));
+    JB_CHECK(cudaEventElapsedTime(&c, e->ev[4 * e->Nr], e->ev[4 * e->Nr + 1]));
     e->prof_tail_ms = c;
   }
   return JB_OK;
@@ -620,14 +682,11 @@ int jb_engine_set_profiling(JbEngine* e, int on) {
   return JB_OK;
 }
 
-int jb_engine_phase_times(JbEngine* e, double* k1_ms, double* step_ms, double* tail_ms) {
-  *k1_ms = e->prof_k1_ms;
-  *step_ms = e->prof_step_ms;
+int jb_engine_phase_times(JbEngine* e, double* seg_ms /* [4] */, double* tail_ms) {
+  for (int k = 0; k < 4; ++k) seg_ms[k] = e->prof_ms[k];
   *tail_ms = e->prof_tail_ms;
   return JB_OK;
 }
-
-double jb_engine_wait_ms(JbEngine* e) { return e->prof_wait_ms; }
 
 int jb_engine_status(JbEngine* e, void* stream) {
   JB_CHECK(cudaSetDevice(e->cfg.device));

@@ -32,24 +32,44 @@ struct StepParams {
   const double* invbuf;
   const JbStepInfo* stepinfo;
   const JbCtl* ctl;
-  double* rowbuf_peers[JB_MAX_RANKS];     // rowbuf[par] on every rank
-  uint32_t* rowflag_peers[JB_MAX_RANKS];  // rowflag[par] on every rank
-  double* swapbuf_peers[JB_MAX_RANKS];
+  double* rowbuf_peers[JB_MAX_RANKS];     // rowbuf[par(t)] on every rank
+  uint32_t* rowflag_peers[JB_MAX_RANKS];  // rowflag[par(t)] on every rank
+  double* swapbuf_peers[JB_MAX_RANKS];    // swapbuf[par(t)] on every rank
   uint32_t* swapflag_peers[JB_MAX_RANKS];
-  double* rowbuf_mc;      // NVLS multicast alias of rowbuf[par] (nullptr -> unicast peer stores)
-  uint32_t* rowflag_mc;   // NVLS multicast alias of rowflag[par]
+  double* rowbuf_mc;      // NVLS multicast alias of rowbuf[par(t)] (nullptr -> unicast peer stores)
+  uint32_t* rowflag_mc;   // NVLS multicast alias of rowflag[par(t)]
+  // SCALE context: the step whose pivot row the SCALE items of this launch produce.  sc_t == t in
+  // the serial schedule and the step-0 prologue; sc_t == t + 1 in phase B2 (pivot-row look-ahead:
+  // the owner of the NEXT pivot row scales and broadcasts it while step t is still being applied).
+  double* sc_rowbuf_peers[JB_MAX_RANKS];
+  uint32_t* sc_rowflag_peers[JB_MAX_RANKS];
+  double* sc_rowbuf_mc;
+  uint32_t* sc_rowflag_mc;
+  int sc_t;
+  uint32_t* prowflag;     // [CT][nsub] local: tag of the last step whose update reached this tile of
+                          // the NEXT pivot row (written by the UPDP items of phase B2)
   int64_t ldw;
   int m, Kp, p, rank, t;
   int rloc, nsub, CT;
   int t_slot;             // local slot of block row t on its owner, else -1
   uint32_t row_expect;    // rowflag value meaning "tile landed"
   uint32_t tag;           // swapflag value for this step
-  int phase;              // JB_PHASE_ALL / _A / _B (look-ahead split)
+  int phase;              // JB_PHASE_*
   int pct0, pct1;         // priority column tiles (cover block column t+1); empty if pct1 < pct0
+  int nb1;                // look-ahead: the first nb1 non-priority column tiles belong to phase B1
+  int has_next;           // phase B2: stepinfo[t + 1] is valid (t + 1 < Nr)
   uint32_t* counter;      // work-item counter of THIS launch (zeroed by the host)
   int only_swapped;       // phase B in tcgen05 mode: only the swapped-in block row stays on the fp64 path
 };
-enum { JB_PHASE_ALL = 0, JB_PHASE_A = 1, JB_PHASE_B = 2, JB_PHASE_A2 = 3 };
+// Work-list phases (csrc/step_plan.h):
+//   ALL  serial schedule: SCALE(t) + ROWT(t) + UPD(t) over every column tile
+//   S    SCALE(t) over every column tile (prologue of the look-ahead schedule, t = 0)
+//   A    ROWT(t) + UPD(t) of the priority column tiles (what K1(t+1) needs)
+//   B1   ROWT(t) of the remaining tiles + UPD(t) of the first nb1 of them (K1(t+1) runs beside it)
+//   B2   after K1(t+1): UPD(t) of the next pivot row first, SCALE(t+1) of every tile, rest of UPD(t)
+//   A2/B tcgen05 mode: SCALE + ROWT of every tile / fp64 update of the swapped-in row only
+enum { JB_PHASE_ALL = 0, JB_PHASE_A = 1, JB_PHASE_B = 2, JB_PHASE_A2 = 3, JB_PHASE_S = 4,
+       JB_PHASE_B1 = 5, JB_PHASE_B2 = 6 };
 struct StepMaps {
   CUtensorMap tmW;     // W              box {JB_RS, JB_BK}
   CUtensorMap tmRow;   // rowbuf[par]    box {JB_RS, JB_BK}

@@ -41,11 +41,61 @@ __device__ __forceinline__ void st_f64x2(double* p, double x, double y) {
   *reinterpret_cast<double2*>(p) = make_double2(x, y);
 }
 
-// kUpdOnly = true is the phase-B specialisation: only UPD items exist, so the SCALE / ROWT code is
-// compiled out and cannot disturb the register allocation of the DMMA loop.
-template <bool kUpdOnly>
+// ---- K4: swap + install the scaled pivot row as block row t (one 64-row chunk per item).
+//      Thread -> (column pair v, row parity); 4 independent 16-byte loads in flight per thread.
+//      Not inlined: its address arithmetic must not compete for registers with the DMMA loop.
+__device__ __noinline__ void rowt_item(double* wrow, double* swap_dst, uint32_t* swap_flag,
+                                       const double* src, const uint32_t* row_flag, uint32_t row_expect,
+                                       uint32_t tag, int rows_valid, int ncol, int64_t ldw,
+                                       int* abort_flag, unsigned long long spin_to) {
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int vec_per_row = ncol / 2;
+  const int v = tid & 63, rh = tid >> 6;
+  const bool vok = v < vec_per_row;
+  wrow += 2 * v;
+  src += 2 * v;
+  if (swap_dst) {
+    // the old block row t goes to the pivot owner's swap buffer over NVLink (main.cpp:1100-1131)
+    double* dst = swap_dst + 2 * v;
+    for (int r0 = rh; r0 < rows_valid; r0 += 8) {
+      double2 x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        x[u] = make_double2(0.0, 0.0);
+        if (vok && r0 + 2 * u < rows_valid) x[u] = ld_f64x2(wrow + (int64_t)(r0 + 2 * u) * ldw);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (vok && r0 + 2 * u < rows_valid) st_f64x2(dst + (int64_t)(r0 + 2 * u) * ldw, x[u].x, x[u].y);
+    }
+    __threadfence_system();
+    named_bar_sync(1, MMA_WARPS * 32);
+    if (tid == 0) st_release_sys_u32(swap_flag, tag);
+  }
+  if (lane == 0) wait_flag_ge(row_flag, row_expect, abort_flag, spin_to);
+  __syncwarp();
+  for (int r0 = rh; r0 < rows_valid; r0 += 8) {
+    double2 x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      x[u] = make_double2(0.0, 0.0);
+      if (vok && r0 + 2 * u < rows_valid) x[u] = ld_f64x2(src + (int64_t)(r0 + 2 * u) * ldw);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (vok && r0 + 2 * u < rows_valid)
+        st_f64x2(wrow + (int64_t)(r0 + 2 * u) * ldw, -x[u].x, -x[u].y);  // rowbuf holds -R
+  }
+}
+
+// kMode selects which item kinds a launch can contain (bit 0: SCALE, bit 1: ROWT; UPD always), so
+// that code a phase never runs is compiled out and cannot disturb the register allocation of the
+// DMMA loop:  0 = B (tcgen05 mode), 1 = S / B2, 2 = A / B1, 3 = ALL / A2.
+template <int kMode>
 __global__ void __launch_bounds__(STEP_THREADS, 2)
 k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
+  constexpr bool kScale = (kMode & 1) != 0;
+  constexpr bool kRowt = (kMode & 2) != 0;
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t full_bar[JB_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[JB_STAGES];
@@ -64,8 +114,11 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   int* const abort_flag = const_cast<int*>(&P.ctl->timeout_flag);
   const unsigned long long spin_to = P.ctl->spin_timeout_ns;
   const JbStepInfo si = P.stepinfo[P.t];
-  const Plan pl = make_plan(P, si);
+  // phase B2 works for two steps at once: UPD items belong to step t, SCALE items to step t + 1
+  const JbStepInfo sn = (kScale && P.phase == JB_PHASE_B2 && P.has_next) ? P.stepinfo[P.t + 1] : si;
+  const Plan pl = make_plan(P, si, sn);
   if (pl.total == 0) return;
+  const int sc_slot = (P.sc_t == P.t) ? si.piv_slot : sn.piv_slot;  // pivot row the SCALE items read
 
 #ifdef JB_DBG_GENERIC
   unsigned char* stage_base =
@@ -89,6 +142,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
 
   const int KC = P.Kp / JB_BK;
   const int col_t0 = P.t * P.m, col_t1 = col_t0 + P.m;  // column slot of step t
+  const int sc_col_t0 = P.sc_t * P.m, sc_col_t1 = sc_col_t0 + P.m;  // ... of the SCALE items' step
   double* const rowbuf_local = P.rowbuf_peers[P.rank];
   const uint32_t* const rowflag_local = P.rowflag_peers[P.rank];
   double* const swapbuf_local = P.swapbuf_peers[P.rank];
@@ -112,15 +166,26 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         ring_item[slot] = idx;
         mbar_arrive(&ring_full[slot]);  // release: publishes ring_item[slot]
         if (idx >= pl.total) break;
-        const Item it = decode(P, si, pl, idx);
-        if (!kUpdOnly && it.type == IT_ROWT) continue;
+        const Item it = decode(P, si, sn, pl, idx);
+        if (kRowt && it.type == IT_ROWT) continue;
         if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;  // tcgen05 mode: the rest is done there
         const int col0 = it.ct * JB_BN;
-        if (kUpdOnly || it.type != IT_SCALE) {
+        if (!kScale || it.type != IT_SCALE) {
           wait_flag_ge(rowflag_local + it.ct, P.row_expect, abort_flag, spin_to);  // pivot-row tile landed
           if (it.type == IT_UPD_SWAPPED)
             for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c * P.nsub + it.sub, P.tag, abort_flag, spin_to);
           fence_proxy_async();  // remote generic-proxy writes -> my async-proxy (TMA) reads
+        } else if (P.phase == JB_PHASE_B2) {
+          // SCALE(t+1) reads the next pivot row as left by UPD(t).  Tiles of phases A / B1 were
+          // finished by earlier launches; the tiles of THIS phase are the UPDP items at the head of
+          // the work list (lower claim index, hence running): wait for their stores.
+          const bool pri = pl.npri > 0 && it.ct >= P.pct0 && it.ct <= P.pct1;
+          const int pos = it.ct < P.pct0 ? it.ct : it.ct - pl.npri;
+          if (!pri && pos >= pl.c0) {
+            for (int sb = 0; sb < P.nsub; ++sb)
+              wait_flag_ge(P.prowflag + it.ct * P.nsub + sb, P.tag, abort_flag, spin_to);
+            fence_proxy_async();  // other CTAs' generic-proxy stores -> my TMA reads of W
+          }
         }
         for (int c = 0; c < KC; ++c, ++it_cnt) {
           const int s = it_cnt % JB_STAGES;
@@ -129,9 +194,9 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           unsigned char* sb = stage_base + (size_t)s * STAGE_BYTES;
           mbar_expect_tx(&full_bar[s], STAGE_BYTES);
           const int k0 = c * JB_BK;
-          if (!kUpdOnly && it.type == IT_SCALE) {
-            tma_load_2d(sb, &M.tmInv, k0, si.piv_slot * P.Kp + it.sub * JB_BM, &full_bar[s]);
-            tma_load_2d(sb + L_BYTES, &M.tmW, col0, si.piv_slot * P.m + k0, &full_bar[s]);
+          if (kScale && it.type == IT_SCALE) {
+            tma_load_2d(sb, &M.tmInv, k0, sc_slot * P.Kp + it.sub * JB_BM, &full_bar[s]);
+            tma_load_2d(sb + L_BYTES, &M.tmW, col0, sc_slot * P.m + k0, &full_bar[s]);
           } else if (it.type == IT_UPD) {
             tma_load_2d(sb, &M.tmL, k0, it.lrow0, &full_bar[s]);
             tma_load_2d(sb + L_BYTES, &M.tmRow, col0, k0, &full_bar[s]);
@@ -157,55 +222,25 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
     __syncwarp();
     if (lane == 0) mbar_arrive(&ring_empty[rslot]);
     if (idx >= pl.total) break;
-    const Item it = decode(P, si, pl, idx);
+    const Item it = decode(P, si, sn, pl, idx);
     const int col0 = it.ct * JB_BN;
     if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;
 
-    if (!kUpdOnly && it.type == IT_ROWT) {
-      // ---- K4: swap + install the scaled pivot row as block row t (one 64-row chunk per item).
-      //      Thread -> (column pair v, row parity); 4 independent 16-byte loads in flight per thread.
+    if (kRowt && it.type == IT_ROWT) {
       const int ncol = (int)min((int64_t)JB_BN, P.ldw - col0);  // multiple of 16
-      const int vec_per_row = ncol / 2;
-      const int v = tid & 63, rh = tid >> 6;
-      const bool vok = v < vec_per_row;
-      const int64_t roff = (int64_t)(it.sub * JB_BM) * P.ldw + col0 + 2 * v;
-      double* wrow = P.W + (int64_t)P.t_slot * P.m * P.ldw + roff;
-      if (si.do_swap) {
-        double* dst = P.swapbuf_peers[si.piv_rank] + roff;
-        for (int r0 = rh; r0 < it.rows_valid; r0 += 8) {
-          double2 x[4];
-#pragma unroll
-          for (int u = 0; u < 4; ++u)
-            if (vok && r0 + 2 * u < it.rows_valid) x[u] = ld_f64x2(wrow + (int64_t)(r0 + 2 * u) * P.ldw);
-#pragma unroll
-          for (int u = 0; u < 4; ++u)
-            if (vok && r0 + 2 * u < it.rows_valid)
-              st_f64x2(dst + (int64_t)(r0 + 2 * u) * P.ldw, x[u].x, x[u].y);
-        }
-        __threadfence_system();
-        named_bar_sync(1, MMA_WARPS * 32);
-        if (tid == 0) st_release_sys_u32(P.swapflag_peers[si.piv_rank] + it.ct * P.nsub + it.sub, P.tag);
-      }
-      if (lane == 0) wait_flag_ge(rowflag_local + it.ct, P.row_expect, abort_flag, spin_to);
-      __syncwarp();
-      const double* src = rowbuf_local + roff;
-      for (int r0 = rh; r0 < it.rows_valid; r0 += 8) {
-        double2 x[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (vok && r0 + 2 * u < it.rows_valid) x[u] = ld_f64x2(src + (int64_t)(r0 + 2 * u) * P.ldw);
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (vok && r0 + 2 * u < it.rows_valid)
-            st_f64x2(wrow + (int64_t)(r0 + 2 * u) * P.ldw, -x[u].x, -x[u].y);  // rowbuf holds -R
-      }
+      const int64_t roff = (int64_t)(it.sub * JB_BM) * P.ldw + col0;
+      rowt_item(P.W + (int64_t)P.t_slot * P.m * P.ldw + roff,
+                si.do_swap ? P.swapbuf_peers[si.piv_rank] + roff : nullptr,
+                si.do_swap ? P.swapflag_peers[si.piv_rank] + it.ct * P.nsub + it.sub : nullptr,
+                rowbuf_local + roff, rowflag_local + it.ct, P.row_expect, P.tag, it.rows_valid, ncol,
+                P.ldw, abort_flag, spin_to);
       continue;
     }
 
     // ---- accumulator init
     double acc[8][4][2];
-    const bool upd = kUpdOnly || (it.type != IT_SCALE);
-    if (!kUpdOnly && it.type == IT_SCALE) {
+    const bool upd = !kScale || (it.type != IT_SCALE);
+    if (kScale && it.type == IT_SCALE) {
 #pragma unroll
       for (int mt = 0; mt < 8; ++mt)
 #pragma unroll
@@ -283,9 +318,14 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           }
         }
       }
-    } else {
+      if (kScale && it.prow) {  // this tile of the next pivot row now carries update t: release SCALE(t+1)
+        __threadfence();
+        named_bar_sync(1, MMA_WARPS * 32);
+        if (tid == 0) st_release_sys_u32(P.prowflag + it.ct * P.nsub + it.sub, P.tag);
+      }
+    } else if (kScale) {
       // SCALE: column slot t of the pivot row is P^-1 itself; broadcast the tile to all ranks
-      const double* pinv = P.invbuf + (int64_t)si.piv_slot * P.Kp * P.Kp;
+      const double* pinv = P.invbuf + (int64_t)sc_slot * P.Kp * P.Kp;
 #pragma unroll
       for (int mt = 0; mt < 8; ++mt) {
         const int r = it.sub * JB_BM + mt * 8 + g;  // row inside the pivot block
@@ -296,14 +336,14 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
             if (c < P.ldw) {
               // the buffer holds -R so the update is a plain accumulate C += L * (-R)
               double x = -acc[mt][nt][0], y = -acc[mt][nt][1];
-              if (c >= col_t0 && c < col_t1) x = -pinv[(int64_t)r * P.Kp + (c - col_t0)];
-              if (c + 1 >= col_t0 && c + 1 < col_t1) y = -pinv[(int64_t)r * P.Kp + (c + 1 - col_t0)];
+              if (c >= sc_col_t0 && c < sc_col_t1) x = -pinv[(int64_t)r * P.Kp + (c - sc_col_t0)];
+              if (c + 1 >= sc_col_t0 && c + 1 < sc_col_t1) y = -pinv[(int64_t)r * P.Kp + (c + 1 - sc_col_t0)];
               const int64_t off = (int64_t)r * P.ldw + c;
-              if (P.rowbuf_mc) {
-                multimem_st_v2f64(P.rowbuf_mc + off, x, y);
+              if (P.sc_rowbuf_mc) {
+                multimem_st_v2f64(P.sc_rowbuf_mc + off, x, y);
               } else {
 #pragma unroll 1
-                for (int q = 0; q < P.p; ++q) st_f64x2(P.rowbuf_peers[q] + off, x, y);
+                for (int q = 0; q < P.p; ++q) st_f64x2(P.sc_rowbuf_peers[q] + off, x, y);
               }
             }
           }
@@ -312,11 +352,11 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
       __threadfence_system();
       named_bar_sync(1, MMA_WARPS * 32);
       if (tid == 0) {
-        if (P.rowflag_mc) {
-          multimem_red_release_add_u32(P.rowflag_mc + it.ct, 1u);
+        if (P.sc_rowflag_mc) {
+          multimem_red_release_add_u32(P.sc_rowflag_mc + it.ct, 1u);
         } else {
 #pragma unroll 1
-          for (int q = 0; q < P.p; ++q) red_release_sys_add_u32(P.rowflag_peers[q] + it.ct, 1u);
+          for (int q = 0; q < P.p; ++q) red_release_sys_add_u32(P.sc_rowflag_peers[q] + it.ct, 1u);
         }
       }
     }
@@ -327,22 +367,28 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
 
 size_t jb_step_smem_bytes() { return (size_t)JB_STAGES * STAGE_BYTES; }
 
-cudaError_t jb_launch_step(const StepParams& P, const StepMaps& M, int grid, cudaStream_t st) {
+template <int kMode>
+static cudaError_t launch_mode(const StepParams& P, const StepMaps& M, int grid, cudaStream_t st) {
   static bool configured[JB_MAX_RANKS] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev % JB_MAX_RANKS]) {
-    cudaError_t e = cudaFuncSetAttribute(k_step_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(k_step_fused<kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)jb_step_smem_bytes());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_step_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)jb_step_smem_bytes());
     if (e != cudaSuccess) return e;
     configured[dev % JB_MAX_RANKS] = true;
   }
-  if (P.phase == JB_PHASE_B)
-    k_step_fused<true><<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
-  else
-    k_step_fused<false><<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
+  k_step_fused<kMode><<<grid, STEP_THREADS, jb_step_smem_bytes(), st>>>(P, M);
   return cudaGetLastError();
+}
+
+cudaError_t jb_launch_step(const StepParams& P, const StepMaps& M, int grid, cudaStream_t st) {
+  switch (P.phase) {
+    case JB_PHASE_B: return launch_mode<0>(P, M, grid, st);
+    case JB_PHASE_S:
+    case JB_PHASE_B2: return launch_mode<1>(P, M, grid, st);
+    case JB_PHASE_A:
+    case JB_PHASE_B1: return launch_mode<2>(P, M, grid, st);
+    default: return launch_mode<3>(P, M, grid, st);
+  }
 }

@@ -22,78 +22,143 @@ struct Item {
   int sub;         // 64-row sub tile inside the block row
   int lrow0;       // first local row of the tile in W (output rows / C rows)
   int rows_valid;  // <= JB_BM
+  int prow;        // UPD item of the NEXT pivot row (phase B2): publishes prowflag when stored
 };
 
 struct Plan {
-  int nscale, nrowt, nupd, total;
-  int rtu;   // row tiles taking part in UPD
-  int npri;  // priority column tiles (they cover block column t+1, needed first by K1(t+1))
+  int nupdp, nscale, nrowt, nupd, total;
+  int rtu;     // row tiles taking part in UPD of step t on this rank
+  int rtu2;    // row tiles of the bulk UPD list of this phase (B2 on the next owner: rtu - nsub)
+  int npri;    // priority column tiles (they cover block columns t and t+1)
+  int nnp;     // non-priority column tiles
+  int c0, c1;  // non-priority positions [c0, c1) whose UPD items belong to this phase
+  int skip_a, skip_b;  // block-row slots left out of the bulk UPD list, ascending, -1 = none
 };
 
-// Work list per phase (items are claimed IN ORDER from a global counter, so anything an item waits
-// for inside the same launch has a lower index and is already running):
-//   ALL : SCALE, ROWT, UPD over every column tile                        (no look-ahead)
-//   A   : SCALE + ROWT + UPD of the PRIORITY column tiles only (block column t+1): the minimum that
-//         K1(t+1) needs, so the pivot search of the next step can start after a ~30 us kernel
-//   A2  : SCALE + ROWT of all other column tiles (owner of the pivot row / of row t only)
-//   B   : UPD of all other column tiles; runs right behind A2 and is flag-synchronised with it tile
-//         by tile, also across GPUs, while K1(t+1) runs beside it on another stream
-JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si) {
+// Work list per phase.  Items are claimed IN ORDER from a global counter, so anything an item waits
+// for inside the same launch has a lower index and is already running.
+//
+// Serial schedule (no look-ahead):
+//   ALL : SCALE(t), ROWT(t), UPD(t) over every column tile
+// Look-ahead schedule, per step t (the pivot row of step t was scaled and broadcast EARLIER, by
+// phase B2 of step t-1, or by the S prologue for t = 0):
+//   A   : ROWT(t) + UPD(t) of the PRIORITY column tiles: the minimum K1(t+1) needs, so the pivot
+//         search of the next step starts after a short kernel
+//   B1  : ROWT(t) of the other column tiles, UPD(t) of the first nb1 of them; K1(t+1) runs beside
+//         it on a high-priority stream
+//   B2  : launched once K1(t+1) has chosen the next pivot row.  On its owner: UPD(t) of that row's
+//         remaining tiles first (UPDP), then SCALE(t+1) of EVERY column tile straight into all
+//         ranks' pivot-row buffers of step t+1 - the broadcast of step t+1 overlaps the bulk of
+//         step t - then, on every rank, the rest of UPD(t).
+// tcgen05 mode keeps A2 (SCALE(t) + ROWT(t) of every tile) and B (fp64 update of the swapped-in
+// row only).
+JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo& sn) {
   Plan pl;
-  pl.npri = (P.phase == JB_PHASE_ALL || P.pct1 < P.pct0) ? 0 : (P.pct1 - P.pct0 + 1);
+  const int ph = P.phase;
+  pl.npri = (ph == JB_PHASE_ALL || ph == JB_PHASE_S || P.pct1 < P.pct0) ? 0 : (P.pct1 - P.pct0 + 1);
+  pl.nnp = P.CT - pl.npri;
   pl.rtu = (P.rloc - (P.t_slot >= 0 ? 1 : 0)) * P.nsub;
+  pl.rtu2 = pl.rtu;
+  pl.skip_a = P.t_slot;
+  pl.skip_b = -1;
   const bool owner = (si.piv_rank == P.rank);
   const bool has_t = (P.t_slot >= 0);
-  int cts = P.CT;  // column tiles this phase scales / installs
-  if (P.phase == JB_PHASE_A) cts = pl.npri;
-  else if (P.phase == JB_PHASE_A2) cts = P.CT - pl.npri;
-  if (P.phase == JB_PHASE_B) {
-    pl.nscale = 0;
-    pl.nrowt = 0;
-    pl.nupd = pl.rtu * (P.CT - pl.npri);
-  } else {
-    pl.nscale = owner ? P.nsub * cts : 0;
-    pl.nrowt = has_t ? P.nsub * cts : 0;
-    pl.nupd = (P.phase == JB_PHASE_A2) ? 0 : pl.rtu * (P.phase == JB_PHASE_ALL ? P.CT : pl.npri);
+  pl.nupdp = pl.nscale = pl.nrowt = 0;
+  pl.c0 = 0;
+  pl.c1 = 0;
+  int ucols = 0;  // column tiles of the bulk UPD list
+  if (ph == JB_PHASE_ALL) {
+    pl.nscale = owner ? P.nsub * P.CT : 0;
+    pl.nrowt = has_t ? P.nsub * P.CT : 0;
+    pl.c1 = pl.nnp;
+    ucols = pl.nnp;
+  } else if (ph == JB_PHASE_S) {
+    pl.nscale = owner ? P.nsub * P.CT : 0;
+  } else if (ph == JB_PHASE_A) {
+    pl.nrowt = has_t ? P.nsub * pl.npri : 0;
+    ucols = pl.npri;
+  } else if (ph == JB_PHASE_A2) {
+    pl.nscale = owner ? P.nsub * pl.nnp : 0;
+    pl.nrowt = has_t ? P.nsub * pl.nnp : 0;
+  } else if (ph == JB_PHASE_B) {
+    pl.c1 = pl.nnp;
+    ucols = pl.nnp;
+  } else if (ph == JB_PHASE_B1) {
+    pl.nrowt = has_t ? P.nsub * pl.nnp : 0;
+    pl.c1 = P.nb1 < pl.nnp ? P.nb1 : pl.nnp;
+    ucols = pl.c1;
+  } else {  // JB_PHASE_B2
+    pl.c0 = P.nb1 < pl.nnp ? P.nb1 : pl.nnp;
+    pl.c1 = pl.nnp;
+    ucols = pl.c1 - pl.c0;
+    if (P.has_next && sn.piv_rank == P.rank) {
+      pl.nupdp = P.nsub * ucols;
+      pl.nscale = P.nsub * P.CT;
+      pl.rtu2 = pl.rtu - P.nsub;
+      // two slots are left out of the bulk list: block row t (ROWT) and the next pivot row (UPDP)
+      if (pl.skip_a < 0 || sn.piv_slot < pl.skip_a) {
+        pl.skip_b = pl.skip_a;
+        pl.skip_a = sn.piv_slot;
+      } else {
+        pl.skip_b = sn.piv_slot;
+      }
+      if (pl.skip_a < 0) {
+        pl.skip_a = pl.skip_b;
+        pl.skip_b = -1;
+      }
+    }
   }
-  pl.total = pl.nscale + pl.nrowt + pl.nupd;
+  pl.nupd = pl.rtu2 * ucols;
+  pl.total = pl.nupdp + pl.nscale + pl.nrowt + pl.nupd;
   return pl;
 }
 
-// position -> column tile for the SCALE / ROWT items of this phase
-JB_HD int ct_of_pos(const StepParams& P, const Plan& pl, int pos) {
-  if (P.phase == JB_PHASE_A) return P.pct0 + pos;
-  if (P.phase == JB_PHASE_A2) return pos < P.pct0 ? pos : pos + pl.npri;
-  return pos;
+// position among the non-priority column tiles -> column tile
+JB_HD int np_ct(const StepParams& P, const Plan& pl, int pos) {
+  return (pl.npri == 0 || pos < P.pct0) ? pos : pos + pl.npri;
 }
 
-JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const Plan& pl,
-                                       int idx) {
+JB_HD int upd_type(const StepParams& P, const JbStepInfo& si, int slot) {
+  return (si.do_swap && si.piv_rank == P.rank && slot == si.piv_slot) ? IT_UPD_SWAPPED : IT_UPD;
+}
+
+JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const JbStepInfo& sn, const Plan& pl,
+                  int idx) {
   Item it;
-  if (idx < pl.nscale) {
-    it.type = IT_SCALE;
+  it.prow = 0;
+  const int ph = P.phase;
+  if (idx < pl.nupdp) {  // B2: the next pivot row first
     const int pos = idx / P.nsub;
     it.sub = idx - pos * P.nsub;
-    it.ct = ct_of_pos(P, pl, pos);
+    it.ct = np_ct(P, pl, pl.c0 + pos);
+    it.lrow0 = sn.piv_slot * P.m + it.sub * JB_BM;
+    it.type = upd_type(P, si, sn.piv_slot);
+    it.prow = 1;
+  } else if (idx < pl.nupdp + pl.nscale) {
+    it.type = IT_SCALE;
+    const int k = idx - pl.nupdp;
+    const int pos = k / P.nsub;
+    it.sub = k - pos * P.nsub;
+    it.ct = (ph == JB_PHASE_A2) ? np_ct(P, pl, pos) : pos;
     it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
-  } else if (idx < pl.nscale + pl.nrowt) {
+  } else if (idx < pl.nupdp + pl.nscale + pl.nrowt) {
     it.type = IT_ROWT;
-    const int pos = (idx - pl.nscale) / P.nsub;
-    it.sub = (idx - pl.nscale) - pos * P.nsub;
-    it.ct = ct_of_pos(P, pl, pos);
+    const int k = idx - pl.nupdp - pl.nscale;
+    const int pos = k / P.nsub;
+    it.sub = k - pos * P.nsub;
+    it.ct = (ph == JB_PHASE_A) ? P.pct0 + pos : np_ct(P, pl, pos);
     it.lrow0 = P.t_slot * P.m + it.sub * JB_BM;
   } else {
-    int u = idx - pl.nscale - pl.nrowt;
-    const int cpos = u / pl.rtu;
-    int rt = u - cpos * pl.rtu;
-    if (P.phase == JB_PHASE_A) it.ct = P.pct0 + cpos;
-    else if (P.phase == JB_PHASE_B) it.ct = cpos < P.pct0 ? cpos : cpos + pl.npri;
-    else it.ct = cpos;
+    const int u = idx - pl.nupdp - pl.nscale - pl.nrowt;
+    const int cpos = u / pl.rtu2;
+    const int rt = u - cpos * pl.rtu2;
+    it.ct = (ph == JB_PHASE_A) ? P.pct0 + cpos : np_ct(P, pl, pl.c0 + cpos);
     int slot = rt / P.nsub;
     it.sub = rt - slot * P.nsub;
-    if (P.t_slot >= 0 && slot >= P.t_slot) slot += 1;  // skip block row t (handled by ROWT)
+    if (pl.skip_a >= 0 && slot >= pl.skip_a) slot += 1;  // block row t (ROWT) / next pivot row (UPDP)
+    if (pl.skip_b >= 0 && slot >= pl.skip_b) slot += 1;
     it.lrow0 = slot * P.m + it.sub * JB_BM;
-    it.type = (si.do_swap && si.piv_rank == P.rank && slot == si.piv_slot) ? IT_UPD_SWAPPED : IT_UPD;
+    it.type = upd_type(P, si, slot);
   }
   it.rows_valid = ((P.m - it.sub * JB_BM) < JB_BM ? (P.m - it.sub * JB_BM) : JB_BM);
   return it;

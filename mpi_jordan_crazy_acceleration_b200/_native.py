@@ -66,7 +66,8 @@ def _declare_host(lib) -> None:
         "jb_cpu_inverse_block": (C.c_int, [C.c_void_p, C.c_void_p, dbl, i64]),
         "jb_cpu_minloc_fold": (C.c_int, [C.c_void_p, C.c_void_p, i64]),
         "jb_cpu_residual": (dbl, [C.c_void_p, C.c_void_p, i64]),
-        "jb_plan_enumerate": (i64, [i32, i32, i32, i32, i64, i32, i32, i32, i32, i32, i32, i32, C.c_void_p, i64]),
+        "jb_plan_enumerate": (i64, [i32, i32, i32, i32, i64, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32,
+                                    C.c_void_p, i64]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -98,8 +99,7 @@ def _declare_cuda(lib) -> None:
         "jb_engine_pivots": (C.c_int, [vp, vp]),
         "jb_engine_launch_count": (i64, [vp]),
         "jb_engine_set_profiling": (C.c_int, [vp, C.c_int]),
-        "jb_engine_phase_times": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
-        "jb_engine_wait_ms": (C.c_double, [vp]),
+        "jb_engine_phase_times": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "jb_engine_w_ptr": (vp, [vp]),
         "jb_engine_ldw": (i64, [vp]),
         "jb_engine_local_rows": (i64, [vp]),

@@ -50,6 +50,9 @@ class JordanSolver:
             raise RuntimeError("JordanSolver needs a CUDA device; use models.eager.EagerJordan on CPU")
         self.lib = _native.cuda()
         self.comm = comm or Comm()
+        # the reference accepts any m, including m > n (one block row of height n, main.cpp:124-127,
+        # 958): a block never needs to be larger than the matrix
+        m = min(int(m), int(n))
         self.layout = Layout(n, m, self.comm.world, self.comm.rank)
         self.device = torch.cuda.current_device() if device is None else int(device)
         torch.cuda.set_device(self.device)
@@ -60,11 +63,17 @@ class JordanSolver:
                                {"fp64": 0, "tc05": 1}[precision])
         h = C.c_void_p()
         rc = self.lib.jb_engine_create(C.byref(cfg), C.byref(h))
-        # collective allocation vote (main.cpp:371-381)
-        if self.comm.allreduce_sum_int(1 if rc != 0 else 0):
+        msg = self.lib.jb_last_error().decode(errors="replace") if rc != 0 else ""
+        # collective vote (main.cpp:371-381): every rank learns the most severe code
+        worst = -int(self.comm.allreduce_max(float(-rc)))
+        if worst != 0:
             if rc == 0:
                 self.lib.jb_engine_destroy(h)
-            raise MemoryError("Not enough memory!")
+            if worst == _native.JB_ERR_NOMEM:
+                raise MemoryError("Not enough memory!")
+            if worst == _native.JB_ERR_ARG:
+                raise ValueError(msg or f"unsupported configuration n={n} m={m} (another rank rejected it)")
+            raise _native.NativeError(worst, msg or "engine creation failed on another rank")
         self._h = h
         self._symm_tensor = None
         self._symm_handle = None
@@ -169,13 +178,21 @@ class JordanSolver:
         _native.check(self.lib.jb_engine_invert(self._h, self._stream()))
 
     def status(self) -> None:
-        """Synchronise; raises :class:`SingularMatrixError` like the reference's rc -2."""
+        """Synchronise and agree on ONE verdict over the ranks (collective): raises
+        :class:`SingularMatrixError` like the reference's rc -2, or ``NativeError`` with
+        ``JB_ERR_TIMEOUT`` when a cross-GPU wait gave up on any rank.  Either way the step epochs of
+        the ranks are inconsistent afterwards, so every rank resets its flags between two barriers
+        and the engine stays usable."""
         rc = self.lib.jb_engine_status(self._h, self._stream())
-        if rc == _native.JB_ERR_SINGULAR:
-            self.comm.barrier()
+        msg = self.lib.jb_last_error().decode(errors="replace") if rc != 0 else ""
+        worst = -int(self.comm.allreduce_max(float(-rc)))  # also a barrier: every rank's stream is idle
+        if worst in (_native.JB_ERR_SINGULAR, _native.JB_ERR_TIMEOUT):
             _native.check(self.lib.jb_engine_reset_sync(self._h))
             self.comm.barrier()
-        _native.check(rc)
+        if worst == _native.JB_ERR_SINGULAR:
+            raise _native.SingularMatrixError(worst, msg or "singular matrix")
+        if worst != 0:
+            raise _native.NativeError(worst, msg or "a peer rank reported an error")
 
     def invert(self) -> float:
         """Timed inversion: device time of the elimination, max over ranks (main.cpp:427-455)."""
@@ -276,17 +293,20 @@ class JordanSolver:
         _native.check(self.lib.jb_engine_set_profiling(self._h, int(on)))
 
     def phase_times(self) -> dict:
-        """Device time (ms) of the last inversion split into K1 (pivot search + min-loc), the fused
-        step kernels, and the final un-permutation.  Needs ``set_profiling(True)``."""
-        a, b, c = C.c_double(), C.c_double(), C.c_double()
-        _native.check(self.lib.jb_engine_phase_times(self._h, C.byref(a), C.byref(b), C.byref(c)))
-        if os.environ.get("JB_NO_LOOKAHEAD"):
+        """Device time (ms) of the last inversion, split by schedule segment and summed over the
+        steps.  Needs ``set_profiling(True)``."""
+        seg, tail = (C.c_double * 4)(), C.c_double()
+        _native.check(self.lib.jb_engine_phase_times(self._h, seg, C.byref(tail)))
+        if os.environ.get("JB_NO_LOOKAHEAD") or self.layout.Nr == 1:
             # serial schedule: fused step kernel of step t, then K1(t+1)
-            return {"step_ms": a.value, "k1_ms": b.value, "tail_ms": c.value, "lookahead": False}
-        # look-ahead: step_A(t) (scale/broadcast/swap + block column t+1), then step_B(t) with
-        # K1(t+1) running beside it on the high-priority stream
-        return {"stepA_ms": a.value, "stepB_ms": b.value, "k1_wait_ms": float(self.lib.jb_engine_wait_ms(self._h)),
-                "tail_ms": c.value, "lookahead": True}
+            return {"step_ms": seg[0], "k1_ms": seg[2], "tail_ms": tail.value, "lookahead": False}
+        if self.precision == "tc05":
+            return {"scale_swap_ms": seg[0], "tc05_update_ms": seg[1], "k1_ms": seg[2], "tail_ms": tail.value,
+                    "lookahead": False}
+        # look-ahead: A(t) (swap + block columns t, t+1), B1(t) with K1(t+1) beside it, what the main
+        # stream still waits for K1(t+1), B2(t) (next pivot row scaled + broadcast, rest of the update)
+        return {"stepA_ms": seg[0], "stepB1_ms": seg[1], "k1_wait_ms": seg[2], "stepB2_ms": seg[3],
+                "stepB_ms": seg[1] + seg[3], "tail_ms": tail.value, "lookahead": True}
 
     @property
     def launch_count(self) -> int:

@@ -90,17 +90,23 @@ def main():
     os.environ.pop("JB_SPIN_TIMEOUT_MS")
     s.fill_formula(1)
     code = 0
-    if comm.rank != 1:
-        try:
+    try:
+        if comm.rank != 1:
             s.invert_async()
-            s.status()
-        except _native.NativeError as exc:
-            code = exc.code
+        s.status()          # collective verdict: every rank (also the idle one) learns about the timeout
+    except _native.NativeError as exc:
+        code = exc.code
     torch.cuda.synchronize()
     codes = comm.allgather_obj(code)
+    # ... and the engine recovers: status() reset the flags on every rank, a normal inversion follows
+    s.fill_formula(1)
+    s.invert()
+    X = s.gather_inverse()
     if comm.rank == 0:
-        results.append({"case": "watchdog", "codes": codes,
-                        "ok": all(c == _native.JB_ERR_TIMEOUT for i, c in enumerate(codes) if i != 1)})
+        ref = torch.linalg.inv(formula_rows(1, 256, torch.arange(256)))
+        results.append({"case": "watchdog+recover", "codes": codes,
+                        "ok": bool(all(c == _native.JB_ERR_TIMEOUT for c in codes)
+                                   and float((X - ref).abs().max()) < 1e-9 * float(ref.abs().max()))})
     s.close()
     if comm.rank == 0:
         print("MPRESULT " + json.dumps(results), flush=True)
