@@ -78,7 +78,7 @@ struct JbEngine {
   double* Lbuf[2] = {nullptr, nullptr};  // L panel of step t lives in Lbuf[t & 1] (look-ahead)
   uint32_t* counters = nullptr;          // one work-item counter per step-kernel launch
   cudaStream_t hstream = nullptr;        // high-priority stream running K1(t+1) beside step_B(t)
-  cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr};
+  cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr}, evB[2] = {nullptr, nullptr};
   bool lookahead = true;
   // tcgen05 split-precision update (precision = 1)
   bool tc05 = false;
@@ -258,7 +258,8 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
     if (cudaStreamCreateWithPriority(&e->hstream, cudaStreamNonBlocking, hi) != cudaSuccess) e->lookahead = false;
     for (int i = 0; i < 2 && e->lookahead; ++i) {
       if (cudaEventCreateWithFlags(&e->evA[i], cudaEventDisableTiming) != cudaSuccess ||
-          cudaEventCreateWithFlags(&e->evK[i], cudaEventDisableTiming) != cudaSuccess)
+          cudaEventCreateWithFlags(&e->evK[i], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&e->evB[i], cudaEventDisableTiming) != cudaSuccess)
         e->lookahead = false;
     }
   }
@@ -283,6 +284,7 @@ void jb_engine_destroy(JbEngine* e) {
   for (int i = 0; i < 2; ++i) {
     if (e->evA[i]) cudaEventDestroy(e->evA[i]);
     if (e->evK[i]) cudaEventDestroy(e->evK[i]);
+    if (e->evB[i]) cudaEventDestroy(e->evB[i]);
   }
   cudaFree(e->counters);
   cudaFree(e->prowflag);
@@ -614,26 +616,35 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   };
 
   JB_CHECK(launch_k1(0, st));
-  if (la) JB_CHECK(launch_step(0, JB_PHASE_S, st));  // pivot row of step 0: scale + broadcast
+  if (la) {
+    JB_CHECK(launch_step(0, JB_PHASE_S, st));  // pivot row of step 0: scale + broadcast
+    JB_CHECK(cudaEventRecord(e->evB[1], st));
+  }
+  // Look-ahead schedule, two streams.  The critical chain A(t) -> K1(t+1) lives on the internal
+  // high-priority stream, back to back, so K1's CTAs are placed the moment A(t) retires; the bulk
+  // phases B1(t), B2(t) live on the caller's stream behind event waits.  (K1 CTAs - 512 threads,
+  // ~45K registers - cannot share an SM with the persistent step CTAs: if B1 were to follow A on
+  // the same stream it would fill every SM first and K1 would only run after it.)
   for (int64_t t = 0; t < e->Nr; ++t) {
     if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t], st));
     if (la && t + 1 < e->Nr) {
       // A(t): row swap / install + update of block columns t, t+1 (their pivot-row tiles were
-      // broadcast during step t-1)
-      JB_CHECK(launch_step(t, JB_PHASE_A, st));
-      JB_CHECK(cudaEventRecord(e->evA[t & 1], st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
-      // K1(t+1) on the high-priority stream, enqueued BEFORE B1(t) so its CTAs get SMs first
-      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evA[t & 1], 0));
+      // broadcast during step t-1); needs B2(t-1) on this rank
+      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB[(t + 1) & 1], 0));
+      JB_CHECK(launch_step(t, JB_PHASE_A, e->hstream));
+      JB_CHECK(cudaEventRecord(e->evA[t & 1], e->hstream));
       JB_CHECK(launch_k1(t + 1, e->hstream));
       JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
-      JB_CHECK(launch_step(t, JB_PHASE_B1, st));
+      JB_CHECK(cudaStreamWaitEvent(st, e->evA[t & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
+      JB_CHECK(launch_step(t, JB_PHASE_B1, st));  // K1(t+1) runs beside it
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
       JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
       // B2(t): knows pivot(t+1): its owner finishes that row first, scales it and broadcasts it
       // for step t+1 while everybody is still busy with the bulk of step t
       JB_CHECK(launch_step(t, JB_PHASE_B2, st));
+      JB_CHECK(cudaEventRecord(e->evB[t & 1], st));
     } else if (la) {
       JB_CHECK(launch_step(t, JB_PHASE_A, st, /*wide=*/true));  // last step: nothing to look ahead to
       if (e->profile)
