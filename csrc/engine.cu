@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <cmath>
 #include <vector>
 #include "common.cuh"
 #include "engine_types.h"
@@ -78,7 +79,10 @@ struct JbEngine {
   double* Lbuf[2] = {nullptr, nullptr};  // L panel of step t lives in Lbuf[t & 1] (look-ahead)
   uint32_t* counters = nullptr;          // one work-item counter per step-kernel launch
   cudaStream_t hstream = nullptr;        // high-priority stream running K1(t+1) beside step_B(t)
-  cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr}, evB[2] = {nullptr, nullptr};
+  cudaStream_t bstream = nullptr;        // carries B2(t) so it can move in while B1(t) drains
+  cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr};
+  cudaEvent_t evB1[2] = {nullptr, nullptr}, evB2[2] = {nullptr, nullptr};
+  uint32_t* b1sync = nullptr;            // {B1 CTA exit counter, B1 done tag} (look-ahead, see StepParams::b1sync)
   bool lookahead = true;
   // tcgen05 split-precision update (precision = 1)
   bool tc05 = false;
@@ -182,6 +186,7 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[1], (rl + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(4 * e->Nr + 4) * 4);
   if (r == cudaSuccess) r = dmalloc((void**)&e->prowflag, (size_t)e->CT * e->nsub * 4);
+  if (r == cudaSuccess) r = dmalloc((void**)&e->b1sync, 256);
   if (r == cudaSuccess)
     r = dmalloc((void**)&e->invbuf, ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->normbuf, (size_t)std::max(e->rloc, 1) * 8);
@@ -256,10 +261,12 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
     int lo = 0, hi = 0;
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
     if (cudaStreamCreateWithPriority(&e->hstream, cudaStreamNonBlocking, hi) != cudaSuccess) e->lookahead = false;
+    if (cudaStreamCreateWithPriority(&e->bstream, cudaStreamNonBlocking, lo) != cudaSuccess) e->lookahead = false;
     for (int i = 0; i < 2 && e->lookahead; ++i) {
       if (cudaEventCreateWithFlags(&e->evA[i], cudaEventDisableTiming) != cudaSuccess ||
           cudaEventCreateWithFlags(&e->evK[i], cudaEventDisableTiming) != cudaSuccess ||
-          cudaEventCreateWithFlags(&e->evB[i], cudaEventDisableTiming) != cudaSuccess)
+          cudaEventCreateWithFlags(&e->evB1[i], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&e->evB2[i], cudaEventDisableTiming) != cudaSuccess)
         e->lookahead = false;
     }
   }
@@ -281,13 +288,16 @@ void jb_engine_destroy(JbEngine* e) {
         }
   if (e->own_symm && e->symm_peers[e->rank]) cudaFree(e->symm_peers[e->rank]);
   if (e->hstream) cudaStreamDestroy(e->hstream);
+  if (e->bstream) cudaStreamDestroy(e->bstream);
   for (int i = 0; i < 2; ++i) {
     if (e->evA[i]) cudaEventDestroy(e->evA[i]);
     if (e->evK[i]) cudaEventDestroy(e->evK[i]);
-    if (e->evB[i]) cudaEventDestroy(e->evB[i]);
+    if (e->evB1[i]) cudaEventDestroy(e->evB1[i]);
+    if (e->evB2[i]) cudaEventDestroy(e->evB2[i]);
   }
   cudaFree(e->counters);
   cudaFree(e->prowflag);
+  cudaFree(e->b1sync);
   for (int i = 0; i < 2; ++i) {
     for (int kb = 0; kb < 2; ++kb) { cudaFree(e->Lq[i][kb]); cudaFree(e->rscale[i][kb]); }
     cudaFree(e->Rq[i]); cudaFree(e->cscale[i]);
@@ -476,6 +486,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   JB_CHECK(cudaMemsetAsync(e->ctl, 0, offsetof(JbCtl, norm_a), st));
 
   JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(4 * e->Nr + 4) * 4, st));
+  JB_CHECK(cudaMemsetAsync(e->b1sync, 0, 8, st));
   K1Params K;
   K.W = e->W; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
   K.ctl = e->ctl; K.stepinfo = e->stepinfo;
@@ -488,9 +499,10 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   S.W = e->W; S.invbuf = e->invbuf; S.stepinfo = e->stepinfo; S.ctl = e->ctl;
   S.ldw = e->ldw; S.m = e->m; S.Kp = e->Kp; S.p = e->p; S.rank = e->rank;
   S.rloc = e->rloc; S.nsub = e->nsub; S.CT = e->CT; S.prowflag = e->prowflag;
+  S.b1sync = (e->lookahead && e->Nr > 1 && !e->tc05) ? e->b1sync : nullptr;
   const int grid = 2 * e->sm_count;
   const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
-  const size_t nev = (size_t)(4 * e->Nr + 2);
+  const size_t nev = (size_t)(6 * e->Nr + 2);
   if (e->profile && e->ev.size() < nev) {
     size_t old = e->ev.size();
     e->ev.resize(nev);
@@ -504,9 +516,10 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   // plus the skew between ranks; everything after it (phase B2) already knows the next pivot.
   double frac = e->b1_frac;
   if (frac < 0) {
-    const double k1_us = (e->m > 128 ? 2.6 : 1.5) * e->m + 20.0;
+    const double waves = std::max(1.0, std::ceil(e->rloc / 128.0));  // candidate CTAs per free SM
+    const double k1_us = ((e->m > 128 ? 2.6 : 1.5) * e->m + 20.0) * waves;
     const double b_us = 2.0 * (double)e->rows_loc * (double)e->ldw * e->m / 30e6;
-    frac = std::max(0.25, std::min(0.85, 1.4 * k1_us / std::max(b_us, 1.0)));
+    frac = std::max(0.03, std::min(0.85, 1.3 * k1_us / std::max(b_us, 1.0)));
   }
 
   // K1 of step t: candidates are the local block rows with global index >= t (main.cpp:1028)
@@ -618,71 +631,97 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   JB_CHECK(launch_k1(0, st));
   if (la) {
     JB_CHECK(launch_step(0, JB_PHASE_S, st));  // pivot row of step 0: scale + broadcast
-    JB_CHECK(cudaEventRecord(e->evB[1], st));
+    JB_CHECK(cudaEventRecord(e->evB1[1], st));
+    JB_CHECK(cudaEventRecord(e->evB2[1], st));
   }
-  // Look-ahead schedule, two streams.  The critical chain A(t) -> K1(t+1) lives on the internal
-  // high-priority stream, back to back, so K1's CTAs are placed the moment A(t) retires; the bulk
-  // phases B1(t), B2(t) live on the caller's stream behind event waits.  (K1 CTAs - 512 threads,
-  // ~45K registers - cannot share an SM with the persistent step CTAs: if B1 were to follow A on
-  // the same stream it would fill every SM first and K1 would only run after it.)
+  // Look-ahead schedule, three streams.
+  //   hstream (high priority): A(t) -> K1(t+1), back to back, so K1's CTAs are placed the moment
+  //       A(t) retires.  (K1 CTAs - 512 threads, ~45K registers - cannot share an SM with the
+  //       persistent step CTAs: a bulk kernel that followed A on the same stream would fill every
+  //       SM first and K1 would only run after it.)
+  //   caller's stream: B1(t), behind A(t).
+  //   bstream: B2(t), behind K1(t+1).  It does not wait for B1(t): the two update disjoint column
+  //       tiles, so B2's CTAs move in as B1's run out of work and no SM idles at that boundary;
+  //       the only data dependency (SCALE(t+1) reads what B1 wrote) is flag-synchronised per tile.
   for (int64_t t = 0; t < e->Nr; ++t) {
-    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t], st));
     if (la && t + 1 < e->Nr) {
       // A(t): row swap / install + update of block columns t, t+1 (their pivot-row tiles were
-      // broadcast during step t-1); needs B2(t-1) on this rank
-      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB[(t + 1) & 1], 0));
+      // broadcast during step t-1); needs all of step t-1 on this rank
+      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB1[(t + 1) & 1], 0));
+      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB2[(t + 1) & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], e->hstream));
       JB_CHECK(launch_step(t, JB_PHASE_A, e->hstream));
       JB_CHECK(cudaEventRecord(e->evA[t & 1], e->hstream));
       JB_CHECK(launch_k1(t + 1, e->hstream));
       JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
       JB_CHECK(cudaStreamWaitEvent(st, e->evA[t & 1], 0));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 1], st));
       JB_CHECK(launch_step(t, JB_PHASE_B1, st));  // K1(t+1) runs beside it
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
-      JB_CHECK(cudaStreamWaitEvent(st, e->evK[t & 1], 0));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
+      JB_CHECK(cudaEventRecord(e->evB1[t & 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 2], st));
       // B2(t): knows pivot(t+1): its owner finishes that row first, scales it and broadcasts it
       // for step t+1 while everybody is still busy with the bulk of step t
-      JB_CHECK(launch_step(t, JB_PHASE_B2, st));
-      JB_CHECK(cudaEventRecord(e->evB[t & 1], st));
+      JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evK[t & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 3], e->bstream));
+      JB_CHECK(launch_step(t, JB_PHASE_B2, e->bstream));
+      JB_CHECK(cudaEventRecord(e->evB2[t & 1], e->bstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 4], e->bstream));
     } else if (la) {
-      JB_CHECK(launch_step(t, JB_PHASE_A, st, /*wide=*/true));  // last step: nothing to look ahead to
+      // last step: nothing to look ahead to; join the streams
+      JB_CHECK(cudaStreamWaitEvent(st, e->evB2[(t + 1) & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], st));
+      JB_CHECK(launch_step(t, JB_PHASE_A, st, /*wide=*/true));
       if (e->profile)
-        for (int k = 1; k <= 3; ++k) JB_CHECK(cudaEventRecord(e->ev[4 * t + k], st));
+        for (int k = 1; k <= 4; ++k) JB_CHECK(cudaEventRecord(e->ev[6 * t + k], st));
     } else if (e->tc05) {
       // A2 with an EMPTY priority range = scale + broadcast + swap only; then the tcgen05 update of
       // everything, then the fp64 kernel for the swapped-in row (if any)
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], st));
       JB_CHECK(launch_step(t, JB_PHASE_A2, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 1], st));
       int rc5 = launch_tc05_b(t, st);
       if (rc5) return rc5;
       JB_CHECK(launch_step(t, JB_PHASE_B, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 2], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 3], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 4], st));
     } else {
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], st));
       JB_CHECK(launch_step(t, JB_PHASE_ALL, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 1], st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 2], st));
+      if (e->profile)
+        for (int k = 1; k <= 3; ++k) JB_CHECK(cudaEventRecord(e->ev[6 * t + k], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * t + 3], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 4], st));
     }
   }
-  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[4 * e->Nr], st));
+  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * e->Nr], st));
   JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
   e->launches += (e->rows_loc > 0);
   if (e->profile) {
-    JB_CHECK(cudaEventRecord(e->ev[4 * e->Nr + 1], st));
+    JB_CHECK(cudaEventRecord(e->ev[6 * e->Nr + 1], st));
     JB_CHECK(cudaStreamSynchronize(st));
+    // kernel durations, summed over the steps.  look-ahead: [0] A(t), [1] B1(t), [2] B2(t).
+    // serial: [0] fused step kernel, [2] K1(t+1).  tcgen05: [0] scale/broadcast/swap, [1] update,
+    // [2] K1(t+1).  [3]: look-ahead only, time B2(t) started after B1(t) had been enqueued to start
+    // (> 0: K1(t+1) took longer than B1 did to drain)
     for (int k = 0; k < 4; ++k) e->prof_ms[k] = 0;
-    for (int64_t t = 0; t < e->Nr; ++t)
-      for (int k = 0; k < 4; ++k) {
-        float x = 0;
-        JB_CHECK(cudaEventElapsedTime(&x, e->ev[4 * t + k], e->ev[4 * t + k + 1]));
-        e->prof_ms[k] += x;
+    for (int64_t t = 0; t < e->Nr; ++t) {
+      float x = 0;
+      const bool two = la && t + 1 < e->Nr;
+      JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t], e->ev[6 * t + 1]));
+      e->prof_ms[0] += x;
+      JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t + 1], e->ev[6 * t + 2]));
+      e->prof_ms[1] += x;
+      JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t + 3], e->ev[6 * t + 4]));
+      e->prof_ms[2] += x;
+      if (two) {
+        JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t + 2], e->ev[6 * t + 3]));
+        e->prof_ms[3] += x;
       }
+    }
     float c = 0;
-    JB_CHECK(cudaEventElapsedTime(&c, e->ev[4 * e->Nr], e->ev[4 * e->Nr + 1]));
+    JB_CHECK(cudaEventElapsedTime(&c, e->ev[6 * e->Nr], e->ev[6 * e->Nr + 1]));
     e->prof_tail_ms = c;
   }
   return JB_OK;

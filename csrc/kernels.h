@@ -48,6 +48,9 @@ struct StepParams {
   int sc_t;
   uint32_t* prowflag;     // [CT][nsub] local: tag of the last step whose update reached this tile of
                           // the NEXT pivot row (written by the UPDP items of phase B2)
+  uint32_t* b1sync;       // local {CTA exit counter, done tag}: the last CTA of phase B1(t) to retire
+                          // publishes tag(t); B2(t), which may run beside B1(t), waits for it before
+                          // SCALE(t+1) touches a column tile B1 updates.  nullptr = not used
   int64_t ldw;
   int m, Kp, p, rank, t;
   int rloc, nsub, CT;

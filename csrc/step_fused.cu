@@ -88,6 +88,15 @@ __device__ __noinline__ void rowt_item(double* wrow, double* swap_dst, uint32_t*
   }
 }
 
+// One thread per retiring CTA of phase B1; the last one publishes "B1(t) done".
+__device__ __forceinline__ void b1_retire(const StepParams& P) {
+  const uint32_t old = atomicAdd(P.b1sync, 1u);
+  if (old == gridDim.x - 1) {
+    P.b1sync[0] = 0;
+    st_release_sys_u32(P.b1sync + 1, P.tag);
+  }
+}
+
 // kMode selects which item kinds a launch can contain (bit 0: SCALE, bit 1: ROWT; UPD always), so
 // that code a phase never runs is compiled out and cannot disturb the register allocation of the
 // DMMA loop:  0 = B (tcgen05 mode), 1 = S / B2, 2 = A / B1, 3 = ALL / A2.
@@ -117,7 +126,10 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   // phase B2 works for two steps at once: UPD items belong to step t, SCALE items to step t + 1
   const JbStepInfo sn = (kScale && P.phase == JB_PHASE_B2 && P.has_next) ? P.stepinfo[P.t + 1] : si;
   const Plan pl = make_plan(P, si, sn);
-  if (pl.total == 0) return;
+  if (pl.total == 0) {
+    if (kRowt && !kScale && P.phase == JB_PHASE_B1 && P.b1sync && tid == 0) b1_retire(P);
+    return;
+  }
   const int sc_slot = (P.sc_t == P.t) ? si.piv_slot : sn.piv_slot;  // pivot row the SCALE items read
 
 #ifdef JB_DBG_GENERIC
@@ -176,16 +188,20 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
             for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c * P.nsub + it.sub, P.tag, abort_flag, spin_to);
           fence_proxy_async();  // remote generic-proxy writes -> my async-proxy (TMA) reads
         } else if (P.phase == JB_PHASE_B2) {
-          // SCALE(t+1) reads the next pivot row as left by UPD(t).  Tiles of phases A / B1 were
-          // finished by earlier launches; the tiles of THIS phase are the UPDP items at the head of
-          // the work list (lower claim index, hence running): wait for their stores.
+          // SCALE(t+1) reads the next pivot row as left by UPD(t).  The tiles of THIS phase are the
+          // UPDP items at the head of the work list (lower claim index, hence running): wait for
+          // their flags.  Priority tiles were finished by phase A (an earlier launch on the way to
+          // K1(t+1)).  The rest belongs to phase B1, which may still be running beside us but never
+          // waits for this launch: wait until its last CTA has retired.
           const bool pri = pl.npri > 0 && it.ct >= P.pct0 && it.ct <= P.pct1;
           const int pos = it.ct < P.pct0 ? it.ct : it.ct - pl.npri;
           if (!pri && pos >= pl.c0) {
             for (int sb = 0; sb < P.nsub; ++sb)
               wait_flag_ge(P.prowflag + it.ct * P.nsub + sb, P.tag, abort_flag, spin_to);
-            fence_proxy_async();  // other CTAs' generic-proxy stores -> my TMA reads of W
+          } else if (!pri && P.b1sync) {
+            wait_flag_ge(P.b1sync + 1, P.tag, abort_flag, spin_to);
           }
+          fence_proxy_async();  // other CTAs' generic-proxy stores -> my TMA reads of W
         }
         for (int c = 0; c < KC; ++c, ++it_cnt) {
           const int s = it_cnt % JB_STAGES;
@@ -360,6 +376,13 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         }
       }
     }
+  }
+  if (kRowt && !kScale && P.phase == JB_PHASE_B1 && P.b1sync) {
+    // B1 only: the last CTA to retire tells B2 (possibly already running beside us) that every
+    // tile of this phase carries update t
+    __threadfence();
+    named_bar_sync(1, MMA_WARPS * 32);
+    if (tid == 0) b1_retire(P);
   }
 }
 

@@ -26,7 +26,7 @@ struct Item {
 };
 
 struct Plan {
-  int nupdp, nscale, nrowt, nupd, total;
+  int nupdp, nscale, nrowt, nupd, nscale2, total;
   int rtu;     // row tiles taking part in UPD of step t on this rank
   int rtu2;    // row tiles of the bulk UPD list of this phase (B2 on the next owner: rtu - nsub)
   int npri;    // priority column tiles (they cover block columns t and t+1)
@@ -46,10 +46,12 @@ struct Plan {
 //         search of the next step starts after a short kernel
 //   B1  : ROWT(t) of the other column tiles, UPD(t) of the first nb1 of them; K1(t+1) runs beside
 //         it on a high-priority stream
-//   B2  : launched once K1(t+1) has chosen the next pivot row.  On its owner: UPD(t) of that row's
-//         remaining tiles first (UPDP), then SCALE(t+1) of EVERY column tile straight into all
-//         ranks' pivot-row buffers of step t+1 - the broadcast of step t+1 overlaps the bulk of
-//         step t - then, on every rank, the rest of UPD(t).
+//   B2  : launched once K1(t+1) has chosen the next pivot row; may run beside the tail of B1.  On
+//         the owner of that row: UPD(t) of the row's tiles of this phase first (UPDP), then
+//         SCALE(t+1) of the priority tiles and of this phase's tiles straight into all ranks'
+//         pivot-row buffers of step t+1 - the broadcast of step t+1 overlaps the bulk of step t -
+//         then, on every rank, the rest of UPD(t); last, on the owner, SCALE(t+1) of the tiles B1
+//         updates (by then B1 has finished them: no CTA sits waiting for another launch).
 // tcgen05 mode keeps A2 (SCALE(t) + ROWT(t) of every tile) and B (fp64 update of the swapped-in
 // row only).
 JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo& sn) {
@@ -63,7 +65,7 @@ JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo
   pl.skip_b = -1;
   const bool owner = (si.piv_rank == P.rank);
   const bool has_t = (P.t_slot >= 0);
-  pl.nupdp = pl.nscale = pl.nrowt = 0;
+  pl.nupdp = pl.nscale = pl.nrowt = pl.nscale2 = 0;
   pl.c0 = 0;
   pl.c1 = 0;
   int ucols = 0;  // column tiles of the bulk UPD list
@@ -93,7 +95,8 @@ JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo
     ucols = pl.c1 - pl.c0;
     if (P.has_next && sn.piv_rank == P.rank) {
       pl.nupdp = P.nsub * ucols;
-      pl.nscale = P.nsub * P.CT;
+      pl.nscale = P.nsub * (pl.npri + ucols);
+      pl.nscale2 = P.nsub * pl.c0;
       pl.rtu2 = pl.rtu - P.nsub;
       // two slots are left out of the bulk list: block row t (ROWT) and the next pivot row (UPDP)
       if (pl.skip_a < 0 || sn.piv_slot < pl.skip_a) {
@@ -109,7 +112,7 @@ JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo
     }
   }
   pl.nupd = pl.rtu2 * ucols;
-  pl.total = pl.nupdp + pl.nscale + pl.nrowt + pl.nupd;
+  pl.total = pl.nupdp + pl.nscale + pl.nrowt + pl.nupd + pl.nscale2;
   return pl;
 }
 
@@ -139,8 +142,18 @@ JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const JbStepInfo& s
     const int k = idx - pl.nupdp;
     const int pos = k / P.nsub;
     it.sub = k - pos * P.nsub;
-    it.ct = (ph == JB_PHASE_A2) ? np_ct(P, pl, pos) : pos;
+    if (ph == JB_PHASE_B2)  // priority tiles first (phase A of the next step needs them), then ours
+      it.ct = pos < pl.npri ? P.pct0 + pos : np_ct(P, pl, pl.c0 + pos - pl.npri);
+    else
+      it.ct = (ph == JB_PHASE_A2) ? np_ct(P, pl, pos) : pos;
     it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
+  } else if (idx >= pl.total - pl.nscale2) {  // B2: SCALE(t+1) of the tiles phase B1 updates
+    it.type = IT_SCALE;
+    const int k = idx - (pl.total - pl.nscale2);
+    const int pos = k / P.nsub;
+    it.sub = k - pos * P.nsub;
+    it.ct = np_ct(P, pl, pos);
+    it.lrow0 = it.sub * JB_BM;
   } else if (idx < pl.nupdp + pl.nscale + pl.nrowt) {
     it.type = IT_ROWT;
     const int k = idx - pl.nupdp - pl.nscale;

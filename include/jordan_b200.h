@@ -115,10 +115,10 @@ int jb_engine_pivots(JbEngine* e, int32_t* piv_out /* Nr */);
 int64_t jb_engine_launch_count(const JbEngine* e); /* kernels launched by this engine so far */
 /* per-kernel CUDA-event timing of the last jb_engine_invert (adds a stream sync; off by default) */
 int jb_engine_set_profiling(JbEngine* e, int on);
-/* seg_ms[4], summed over the steps.  Look-ahead schedule: [0] phase A (swap + block columns t, t+1),
- * [1] phase B1 (K1(t+1) runs beside it), [2] main stream still waiting for K1(t+1), [3] phase B2
- * (next pivot row scaled + broadcast, rest of the update).  Serial schedule: [0] fused step kernel,
- * [2] K1(t+1).  tail_ms: final column un-permutation. */
+/* seg_ms[4], kernel durations summed over the steps.  Look-ahead schedule: [0] phase A (swap +
+ * block columns t, t+1), [1] phase B1 (K1(t+1) runs beside it), [2] phase B2 (next pivot row scaled
+ * + broadcast, rest of the update), [3] start of B2 minus end of B1 (negative: they overlapped).
+ * Serial schedule: [0] fused step kernel, [2] K1(t+1).  tail_ms: final column un-permutation. */
 int jb_engine_phase_times(JbEngine* e, double* seg_ms, double* tail_ms);
 
 /* results */
