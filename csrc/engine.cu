@@ -75,15 +75,21 @@ struct JbEngine {
   int64_t n, Nr, ldw, rows_loc;
   int m, p, rank, Kp, rloc, nsub, CT, sm_count;
   // local buffers
-  double *W = nullptr, *invbuf = nullptr, *normbuf = nullptr, *Acopy = nullptr;
-  double* Lbuf[2] = {nullptr, nullptr};  // L panel of step t lives in Lbuf[t & 1] (look-ahead)
+  double *W = nullptr, *normbuf = nullptr, *Acopy = nullptr;
+  // K1(t+2) may already run while step t is being applied and A(t+1) reads its own panel: the L
+  // panel of step g lives in Lbuf[g % 3], the candidate inverses of step g in invbuf[g & 1]
+  double* Lbuf[3] = {nullptr, nullptr, nullptr};
+  double* invbuf[2] = {nullptr, nullptr};
   uint32_t* counters = nullptr;          // one work-item counter per step-kernel launch
   cudaStream_t hstream = nullptr;        // high-priority stream running K1(t+1) beside step_B(t)
   cudaStream_t bstream = nullptr;        // carries B2(t) so it can move in while B1(t) drains
-  cudaEvent_t evA[2] = {nullptr, nullptr}, evK[2] = {nullptr, nullptr};
+  cudaEvent_t evA = nullptr, evK[2] = {nullptr, nullptr}, evG[2] = {nullptr, nullptr};
   cudaEvent_t evB1[2] = {nullptr, nullptr}, evB2[2] = {nullptr, nullptr};
   uint32_t* b1sync = nullptr;            // {B1 CTA exit counter, B1 done tag} (look-ahead, see StepParams::b1sync)
   bool lookahead = true;
+  bool k1_early = true;    // K1(t+2) pending right behind A(t+1) (JB_K1_GATED=1: released by the end of B2(t))
+  int sched = 0;           // JB_SCHED: 1 = phase A in line (between B2(t-1) and B1(t)), else A beside B2(t-1)
+  bool b2_overlap = true;  // B2 on its own stream (moves in while B1 drains); JB_B2_SERIAL=1: behind B1
   // tcgen05 split-precision update (precision = 1)
   bool tc05 = false;
   int tc_slices = 8;
@@ -107,7 +113,7 @@ struct JbEngine {
   bool peers_opened[3] = {false, false, false};
   const double* W_peers[JB_MAX_RANKS] = {nullptr};
   const double* R_peers[JB_MAX_RANKS] = {nullptr};  // refinement residual slabs (K7)
-  StepMaps maps[2];
+  StepMaps maps[2][6];  // [SCALE context is the next step][global step % 6]
   bool maps_ready = false;
   uint32_t gstep = 0;  // global step counter (same on every rank)
   int64_t launches = 0;
@@ -126,18 +132,22 @@ namespace {
 
 int build_maps(JbEngine* e) {
   unsigned char* loc = e->symm_peers[e->rank];
-  for (int par = 0; par < 2; ++par) {
-    StepMaps& M = e->maps[par];
-    int rc;
-    if ((rc = make_map(&M.tmW, e->W, e->ldw, e->rows_loc, e->ldw, JB_RS, JB_BK))) return rc;
-    if ((rc = make_map(&M.tmRow, loc + e->off_rowbuf[par], e->ldw, e->Kp, e->ldw, JB_RS, JB_BK)))
-      return rc;
-    if ((rc = make_map(&M.tmL, e->Lbuf[par], e->Kp, e->rows_loc, e->Kp, JB_LS, JB_BM))) return rc;
-    if ((rc = make_map(&M.tmInv, e->invbuf, e->Kp, (uint64_t)e->rloc * e->Kp, e->Kp, JB_LS, JB_BM)))
-      return rc;
-    if ((rc = make_map(&M.tmSwap, loc + e->off_swapbuf[par], e->ldw, e->Kp, e->ldw, JB_LS, JB_BM)))
-      return rc;
-  }
+  for (int nx = 0; nx < 2; ++nx)
+    for (int g = 0; g < 6; ++g) {
+      StepMaps& M = e->maps[nx][g];
+      const int par = g & 1;
+      int rc;
+      if ((rc = make_map(&M.tmW, e->W, e->ldw, e->rows_loc, e->ldw, JB_RS, JB_BK))) return rc;
+      if ((rc = make_map(&M.tmRow, loc + e->off_rowbuf[par], e->ldw, e->Kp, e->ldw, JB_RS, JB_BK)))
+        return rc;
+      if ((rc = make_map(&M.tmL, e->Lbuf[g % 3], e->Kp, e->rows_loc, e->Kp, JB_LS, JB_BM))) return rc;
+      // inverse of the pivot block of the step the SCALE items of the launch belong to
+      if ((rc = make_map(&M.tmInv, e->invbuf[(g + nx) & 1], e->Kp, (uint64_t)e->rloc * e->Kp, e->Kp, JB_LS,
+                         JB_BM)))
+        return rc;
+      if ((rc = make_map(&M.tmSwap, loc + e->off_swapbuf[par], e->ldw, e->Kp, e->ldw, JB_LS, JB_BM)))
+        return rc;
+    }
   e->maps_ready = true;
   return JB_OK;
 }
@@ -182,13 +192,13 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   const size_t rl = (size_t)std::max<int64_t>(e->rows_loc, 1);
   cudaError_t r = cudaSuccess;
   if (r == cudaSuccess) r = dmalloc((void**)&e->W, rl * e->ldw * 8);
-  if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[0], (rl + JB_BM) * e->Kp * 8);
-  if (r == cudaSuccess) r = dmalloc((void**)&e->Lbuf[1], (rl + JB_BM) * e->Kp * 8);
+  for (int i = 0; i < 3 && r == cudaSuccess; ++i) r = dmalloc((void**)&e->Lbuf[i], (rl + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->counters, (size_t)(4 * e->Nr + 4) * 4);
   if (r == cudaSuccess) r = dmalloc((void**)&e->prowflag, (size_t)e->CT * e->nsub * 4);
   if (r == cudaSuccess) r = dmalloc((void**)&e->b1sync, 256);
   if (r == cudaSuccess)
-    r = dmalloc((void**)&e->invbuf, ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
+    for (int i = 0; i < 2 && r == cudaSuccess; ++i)
+      r = dmalloc((void**)&e->invbuf[i], ((size_t)std::max(e->rloc, 1) * e->Kp + JB_BM) * e->Kp * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->normbuf, (size_t)std::max(e->rloc, 1) * 8);
   if (r == cudaSuccess) r = dmalloc((void**)&e->okbuf, (size_t)std::max(e->rloc, 1) * 4);
   if (r == cudaSuccess) r = dmalloc((void**)&e->ctl, sizeof(JbCtl));
@@ -257,14 +267,18 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   if (const char* f = getenv("JB_B1_FRAC")) e->b1_frac = std::max(0.0, std::min(1.0, atof(f)));
   if (getenv("JB_TIME_KERNELS")) e->profile = true;
   if (getenv("JB_NO_LOOKAHEAD")) e->lookahead = false;
+  if (getenv("JB_B2_SERIAL")) e->b2_overlap = false;
+  if (getenv("JB_K1_GATED")) e->k1_early = false;
+  if (const char* sc = getenv("JB_SCHED")) e->sched = atoi(sc);
   {
     int lo = 0, hi = 0;
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
     if (cudaStreamCreateWithPriority(&e->hstream, cudaStreamNonBlocking, hi) != cudaSuccess) e->lookahead = false;
     if (cudaStreamCreateWithPriority(&e->bstream, cudaStreamNonBlocking, lo) != cudaSuccess) e->lookahead = false;
     for (int i = 0; i < 2 && e->lookahead; ++i) {
-      if (cudaEventCreateWithFlags(&e->evA[i], cudaEventDisableTiming) != cudaSuccess ||
+      if ((i == 0 && cudaEventCreateWithFlags(&e->evA, cudaEventDisableTiming) != cudaSuccess) ||
           cudaEventCreateWithFlags(&e->evK[i], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&e->evG[i], cudaEventDisableTiming) != cudaSuccess ||
           cudaEventCreateWithFlags(&e->evB1[i], cudaEventDisableTiming) != cudaSuccess ||
           cudaEventCreateWithFlags(&e->evB2[i], cudaEventDisableTiming) != cudaSuccess)
         e->lookahead = false;
@@ -290,8 +304,9 @@ void jb_engine_destroy(JbEngine* e) {
   if (e->hstream) cudaStreamDestroy(e->hstream);
   if (e->bstream) cudaStreamDestroy(e->bstream);
   for (int i = 0; i < 2; ++i) {
-    if (e->evA[i]) cudaEventDestroy(e->evA[i]);
+    if (i == 0 && e->evA) cudaEventDestroy(e->evA);
     if (e->evK[i]) cudaEventDestroy(e->evK[i]);
+    if (e->evG[i]) cudaEventDestroy(e->evG[i]);
     if (e->evB1[i]) cudaEventDestroy(e->evB1[i]);
     if (e->evB2[i]) cudaEventDestroy(e->evB2[i]);
   }
@@ -302,7 +317,8 @@ void jb_engine_destroy(JbEngine* e) {
     for (int kb = 0; kb < 2; ++kb) { cudaFree(e->Lq[i][kb]); cudaFree(e->rscale[i][kb]); }
     cudaFree(e->Rq[i]); cudaFree(e->cscale[i]);
   }
-  cudaFree(e->W); cudaFree(e->Lbuf[0]); cudaFree(e->Lbuf[1]); cudaFree(e->invbuf); cudaFree(e->normbuf); cudaFree(e->okbuf);
+  cudaFree(e->W); cudaFree(e->Lbuf[0]); cudaFree(e->Lbuf[1]); cudaFree(e->Lbuf[2]); cudaFree(e->invbuf[0]);
+  cudaFree(e->invbuf[1]); cudaFree(e->normbuf); cudaFree(e->okbuf);
   cudaFree(e->ctl); cudaFree(e->stepinfo); cudaFree(e->rowsum); cudaFree(e->scratch_max);
   cudaFree(e->Acopy); cudaFree(e->Xp); cudaFree(e->Rslab);
   delete e;
@@ -486,9 +502,9 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   JB_CHECK(cudaMemsetAsync(e->ctl, 0, offsetof(JbCtl, norm_a), st));
 
   JB_CHECK(cudaMemsetAsync(e->counters, 0, (size_t)(4 * e->Nr + 4) * 4, st));
-  JB_CHECK(cudaMemsetAsync(e->b1sync, 0, 8, st));
+  JB_CHECK(cudaMemsetAsync(e->b1sync, 0, 256, st));
   K1Params K;
-  K.W = e->W; K.invbuf = e->invbuf; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
+  K.W = e->W; K.normbuf = e->normbuf; K.okbuf = e->okbuf;
   K.ctl = e->ctl; K.stepinfo = e->stepinfo;
   for (int r = 0; r < JB_MAX_RANKS; ++r)
     K.mail_peers[r] = r < e->p ? (JbMail*)(e->symm_peers[r] + e->off_mail) : nullptr;
@@ -496,13 +512,15 @@ int jb_engine_invert(JbEngine* e, void* stream) {
 
   StepParams S;
   memset(&S, 0, sizeof(S));
-  S.W = e->W; S.invbuf = e->invbuf; S.stepinfo = e->stepinfo; S.ctl = e->ctl;
+  S.W = e->W; S.stepinfo = e->stepinfo; S.ctl = e->ctl;
   S.ldw = e->ldw; S.m = e->m; S.Kp = e->Kp; S.p = e->p; S.rank = e->rank;
   S.rloc = e->rloc; S.nsub = e->nsub; S.CT = e->CT; S.prowflag = e->prowflag;
-  S.b1sync = (e->lookahead && e->Nr > 1 && !e->tc05) ? e->b1sync : nullptr;
+  const bool la = e->lookahead && e->Nr > 1 && !e->tc05;
+  S.b1sync = la ? e->b1sync : nullptr;
+  S.early = e->b1sync + 16;
   const int grid = 2 * e->sm_count;
   const int panel_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(32, (e->rows_loc + 15) / 16));
-  const size_t nev = (size_t)(6 * e->Nr + 2);
+  const size_t nev = (size_t)(8 * e->Nr + 2);
   if (e->profile && e->ev.size() < nev) {
     size_t old = e->ev.size();
     e->ev.resize(nev);
@@ -510,7 +528,6 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   }
   const uint32_t g0 = e->gstep;
   e->gstep += (uint32_t)e->Nr;
-  const bool la = e->lookahead && e->Nr > 1 && !e->tc05;
   // Share of the non-priority column tiles that phase B1 updates while K1(t+1) runs beside it.  B1
   // should last about as long as K1 (~1.5 us per elimination column, 2.6 us with a 4-CTA cluster)
   // plus the skew between ranks; everything after it (phase B2) already knows the next pivot.
@@ -521,6 +538,8 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     const double b_us = 2.0 * (double)e->rows_loc * (double)e->ldw * e->m / 30e6;
     frac = std::max(0.03, std::min(0.85, 1.3 * k1_us / std::max(b_us, 1.0)));
   }
+  auto pri_lo = [&](int64_t t) { return (int)((t * e->m) / JB_BN); };
+  auto pri_hi = [&](int64_t t) { return (int)std::min<int64_t>(e->CT - 1, ((t + 2) * e->m - 1) / JB_BN); };
 
   // K1 of step t: candidates are the local block rows with global index >= t (main.cpp:1028)
   auto launch_k1 = [&](int64_t t, cudaStream_t s) -> cudaError_t {
@@ -531,22 +550,22 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     K.ncand = (int)std::max<int64_t>(0, e->rloc - s0);
     K.ngroups = std::max(K.ncand, 1);
     K.tag = g + 1;
-    K.Lbuf = e->Lbuf[g & 1];
+    K.Lbuf = e->Lbuf[g % 3];
+    K.invbuf = e->invbuf[g & 1];
     e->launches += 1;
     cudaError_t ce = jb_launch_k1(K, panel_ctas, s);
     if (ce == cudaSuccess && e->tc05) {
       // integer slices of the L panel for the tcgen05 update of this step
       for (int kb = 0; kb < e->tc_kb && ce == cudaSuccess; ++kb) {
-        ce = jb_tc05_slice_rows(e->Lbuf[g & 1] + kb * 128, e->Kp, e->rows_loc, std::min(128, e->m - kb * 128),
+        ce = jb_tc05_slice_rows(e->Lbuf[g % 3] + kb * 128, e->Kp, e->rows_loc, std::min(128, e->m - kb * 128),
                                 e->tc_slices, e->Lq[g & 1][kb], e->rows_loc, e->rscale[g & 1][kb], s);
         e->launches += 1;
       }
     }
     return ce;
   };
-  // `wide` = every column tile is a priority tile (last step of the look-ahead schedule: phase A
-  // then is ROWT + UPD of the whole row, nothing is left for B1 / B2)
-  auto launch_step = [&](int64_t t, int phase, cudaStream_t s, bool wide = false) -> cudaError_t {
+  // `wide` = every column tile is a priority tile (A then is ROWT + UPD of the whole row)
+  auto launch_step = [&](int64_t t, int phase, cudaStream_t s, int use_grid, bool wide = false) -> cudaError_t {
     const uint32_t g = g0 + (uint32_t)t;
     const int par = g & 1;
     S.t = (int)t;
@@ -554,9 +573,11 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     S.row_expect = ((g >> 1) + 1) * (uint32_t)e->nsub;
     S.tag = g + 1;
     // SCALE items of phase B2 produce the pivot row of step t + 1 (other buffer parity)
-    S.sc_t = (phase == JB_PHASE_B2) ? (int)t + 1 : (int)t;
+    const int nx = (phase == JB_PHASE_B2) ? 1 : 0;
+    S.sc_t = (int)t + nx;
     S.has_next = (phase == JB_PHASE_B2 && t + 1 < e->Nr) ? 1 : 0;
-    const int spar = (phase == JB_PHASE_B2) ? (par ^ 1) : par;
+    const int spar = par ^ nx;
+    S.invbuf = e->invbuf[spar];
     for (int r = 0; r < JB_MAX_RANKS; ++r) {
       unsigned char* base = r < e->p ? e->symm_peers[r] : nullptr;
       S.rowbuf_peers[r] = base ? (double*)(base + e->off_rowbuf[par]) : nullptr;
@@ -574,18 +595,28 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     // priority column tiles = the ones covering block column t+1 (what K1(t+1) reads)
     // ... plus block column t itself: a swapped-in row takes its L operand from the swap buffer's
     // column block t, so the ROWT pushes of those tiles must be in the same phase
-    S.pct0 = (int)((t * e->m) / JB_BN);
-    S.pct1 = (int)std::min<int64_t>(e->CT - 1, ((t + 2) * e->m - 1) / JB_BN);
-    if (wide) {
+    S.pct0 = pri_lo(t);
+    S.pct1 = pri_hi(t);
+    // phase A of step t > 0 runs beside B2(t-1) / the tail of B1(t-1): tiles outside the previous
+    // priority range are B1(t-1)'s early tiles and are waited for through their flags
+    S.prev_pct0 = t > 0 ? pri_lo(t - 1) : 0;
+    S.prev_pct1 = t > 0 ? pri_hi(t - 1) : e->CT - 1;
+    S.prev_tag = t > 0 ? g : 0;
+    if (wide) {  // everything before this launch has completed: no early-tile flags to wait for
       S.pct0 = 0;
       S.pct1 = e->CT - 1;
+      S.prev_tag = 0;
     }
     if (e->tc05) {  // no priority tiles: phase A2 = scale/broadcast/swap, phase B = swapped-in row
       S.pct0 = 0;
       S.pct1 = -1;
     }
     const int nnp = e->CT - (S.pct1 >= S.pct0 ? S.pct1 - S.pct0 + 1 : 0);
-    S.nb1 = std::min(nnp, (int)(frac * nnp + 0.999));
+    // B1's early tiles: what the priority range of step t+1 adds to the one of step t (block
+    // column t+2); B1 always covers them
+    S.nearly = std::max(0, std::min({nnp, 8, pri_hi(t + 1) - S.pct1}));
+    S.nb1 = std::min(nnp, std::max(S.nearly, (int)(frac * nnp + 0.999)));
+    if (phase == JB_PHASE_B1 && t + 1 >= e->Nr) S.nb1 = nnp;  // last step: B1 is all that is left
     int cslot = 0;
     switch (phase) {
       case JB_PHASE_B: case JB_PHASE_B1: cslot = 1; break;
@@ -596,7 +627,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     S.counter = e->counters + 4 * t + cslot;
     S.only_swapped = (e->tc05 && phase == JB_PHASE_B) ? 1 : 0;
     e->launches += 1;
-    return jb_launch_step(S, e->maps[par], grid, s);
+    return jb_launch_step(S, e->maps[nx][g % 6], use_grid, s);
   };
   // tcgen05 mode: phase B = slice the (negated) pivot row, int8 tensor-core update of every block
   // row except row t and the swapped-in row, which stays on the fp64 kernel (only_swapped)
@@ -628,100 +659,174 @@ int jb_engine_invert(JbEngine* e, void* stream) {
     return JB_OK;
   };
 
-  JB_CHECK(launch_k1(0, st));
-  if (la) {
-    JB_CHECK(launch_step(0, JB_PHASE_S, st));  // pivot row of step 0: scale + broadcast
+  // ---------------------------------------------------------------- look-ahead schedule
+  // Three streams, per step t:
+  //   caller's stream : B1(t)   ROWT(t) of the non-priority tiles + UPD(t) of the first few of them
+  //                             (starting with block column t+2, flagged when done)
+  //   bstream         : B2(t)   launched when K1(t+1) has finished; its CTAs move in while B1(t)
+  //                             drains.  Next pivot row first (UPDP), SCALE(t+1) -> broadcast for
+  //                             step t+1, then the bulk of UPD(t)
+  //   hstream (high)  : A(t+1)  launched together with B2(t) on a small grid: ROWT(t+1) + UPD(t+1)
+  //                             of block columns t+1, t+2 as soon as their pivot-row tiles land;
+  //                     K1(t+2) right behind it: pending at high priority, so its CTAs (which need
+  //                             whole SMs) are placed first when B2(t) retires, before B1(t+1)
+  // The only place where the GPU drains is the end of B2(t); the critical chain
+  // K1 -> SCALE -> A -> K1 runs a full step ahead of the bulk update.
+  const int a_items = (e->rloc * e->nsub) * (pri_hi(1) - pri_lo(1) + 1);
+  // Default: phase A beside B2 of the previous step.  At 8 GPUs A is a fraction of a wave and, run
+  // in line between two bulk kernels, left most SMs idle for ~40 us per step (0.310 s -> 0.301 s);
+  // at 1 GPU the two schedules measure the same.  JB_SCHED=1 selects the in-line variant.
+  const bool a_inline = e->sched == 1;
+  if (la && a_inline) {
+    // hstream: A(t) -> K1(t+1) back to back (K1's CTAs are placed the moment A(t) retires; B1(t)
+    // waits for A(t) across streams, so it cannot fill the SMs first); caller's stream: B1(t);
+    // bstream: B2(t) behind K1(t+1), moving in while B1(t) drains.
+    JB_CHECK(launch_k1(0, st));
+    JB_CHECK(launch_step(0, JB_PHASE_S, st, grid));
     JB_CHECK(cudaEventRecord(e->evB1[1], st));
     JB_CHECK(cudaEventRecord(e->evB2[1], st));
-  }
-  // Look-ahead schedule, three streams.
-  //   hstream (high priority): A(t) -> K1(t+1), back to back, so K1's CTAs are placed the moment
-  //       A(t) retires.  (K1 CTAs - 512 threads, ~45K registers - cannot share an SM with the
-  //       persistent step CTAs: a bulk kernel that followed A on the same stream would fill every
-  //       SM first and K1 would only run after it.)
-  //   caller's stream: B1(t), behind A(t).
-  //   bstream: B2(t), behind K1(t+1).  It does not wait for B1(t): the two update disjoint column
-  //       tiles, so B2's CTAs move in as B1's run out of work and no SM idles at that boundary;
-  //       the only data dependency (SCALE(t+1) reads what B1 wrote) is flag-synchronised per tile.
-  for (int64_t t = 0; t < e->Nr; ++t) {
-    if (la && t + 1 < e->Nr) {
-      // A(t): row swap / install + update of block columns t, t+1 (their pivot-row tiles were
-      // broadcast during step t-1); needs all of step t-1 on this rank
+    for (int64_t t = 0; t + 1 < e->Nr; ++t) {
       JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB1[(t + 1) & 1], 0));
       JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB2[(t + 1) & 1], 0));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], e->hstream));
-      JB_CHECK(launch_step(t, JB_PHASE_A, e->hstream));
-      JB_CHECK(cudaEventRecord(e->evA[t & 1], e->hstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t], e->hstream));
+      JB_CHECK(launch_step(t, JB_PHASE_A, e->hstream, grid));
+      JB_CHECK(cudaEventRecord(e->evG[t & 1], e->hstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 1], e->hstream));
       JB_CHECK(launch_k1(t + 1, e->hstream));
-      JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
-      JB_CHECK(cudaStreamWaitEvent(st, e->evA[t & 1], 0));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 1], st));
-      JB_CHECK(launch_step(t, JB_PHASE_B1, st));  // K1(t+1) runs beside it
+      JB_CHECK(cudaEventRecord(e->evK[(t + 1) & 1], e->hstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 2], e->hstream));
+      JB_CHECK(cudaStreamWaitEvent(st, e->evG[t & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 3], st));
+      JB_CHECK(launch_step(t, JB_PHASE_B1, st, grid));
       JB_CHECK(cudaEventRecord(e->evB1[t & 1], st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 2], st));
-      // B2(t): knows pivot(t+1): its owner finishes that row first, scales it and broadcasts it
-      // for step t+1 while everybody is still busy with the bulk of step t
-      JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evK[t & 1], 0));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 3], e->bstream));
-      JB_CHECK(launch_step(t, JB_PHASE_B2, e->bstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 4], st));
+      JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evK[(t + 1) & 1], 0));
+      if (!e->b2_overlap) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[t & 1], 0));  // JB_B2_SERIAL
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 5], e->bstream));
+      JB_CHECK(launch_step(t, JB_PHASE_B2, e->bstream, grid));
       JB_CHECK(cudaEventRecord(e->evB2[t & 1], e->bstream));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 4], e->bstream));
-    } else if (la) {
-      // last step: nothing to look ahead to; join the streams
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 6], e->bstream));
+    }
+    {  // last step: A over the whole width, nothing to look ahead to
+      const int64_t t = e->Nr - 1;
       JB_CHECK(cudaStreamWaitEvent(st, e->evB2[(t + 1) & 1], 0));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], st));
-      JB_CHECK(launch_step(t, JB_PHASE_A, st, /*wide=*/true));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t], st));
+      JB_CHECK(launch_step(t, JB_PHASE_A, st, grid, /*wide=*/true));
       if (e->profile)
-        for (int k = 1; k <= 4; ++k) JB_CHECK(cudaEventRecord(e->ev[6 * t + k], st));
-    } else if (e->tc05) {
+        for (int k = 1; k <= 6; ++k) JB_CHECK(cudaEventRecord(e->ev[8 * t + k], st));
+    }
+  } else if (la) {
+    const int a_grid = std::max(32, std::min(e->sm_count, a_items / 2));
+    JB_CHECK(launch_k1(0, st));
+    JB_CHECK(launch_step(0, JB_PHASE_S, st, grid));  // pivot row of step 0: scale + broadcast
+    JB_CHECK(cudaEventRecord(e->evG[1], st));
+    // A(0) -> K1(1) back to back on hstream, B1(0) behind A(0): K1(1) gets its SMs first
+    JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evG[1], 0));
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[0], e->hstream));
+    JB_CHECK(launch_step(0, JB_PHASE_A, e->hstream, grid));
+    JB_CHECK(cudaEventRecord(e->evA, e->hstream));
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[1], e->hstream));
+    JB_CHECK(launch_k1(1, e->hstream));
+    JB_CHECK(cudaEventRecord(e->evK[1], e->hstream));
+    if (e->profile) JB_CHECK(cudaEventRecord(e->ev[2], e->hstream));
+    JB_CHECK(cudaStreamWaitEvent(st, e->evA, 0));
+    JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evG[1], 0));
+    for (int64_t t = 0; t + 1 < e->Nr; ++t) {
+      // B1(t) (for t > 0: behind B2(t-1), which ends the previous step on this rank)
+      if (t > 0) JB_CHECK(cudaStreamWaitEvent(st, e->evB2[(t + 1) & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 3], st));
+      JB_CHECK(launch_step(t, JB_PHASE_B1, st, grid));
+      JB_CHECK(cudaEventRecord(e->evB1[t & 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 4], st));
+      // B2(t): needs pivot(t+1); B1(t-1) is long finished (explicit only for the record)
+      JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evK[(t + 1) & 1], 0));
+      if (t > 0) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[(t + 1) & 1], 0));
+      if (!e->b2_overlap) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[t & 1], 0));  // JB_B2_SERIAL
+      JB_CHECK(cudaEventRecord(e->evG[t & 1], e->bstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 5], e->bstream));
+      JB_CHECK(launch_step(t, JB_PHASE_B2, e->bstream, grid));
+      JB_CHECK(cudaEventRecord(e->evB2[t & 1], e->bstream));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 6], e->bstream));
+      // A(t+1) beside B2(t), K1(t+2) behind it
+      JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evG[t & 1], 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * (t + 1)], e->hstream));
+      JB_CHECK(launch_step(t + 1, JB_PHASE_A, e->hstream, a_grid));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * (t + 1) + 1], e->hstream));
+      if (t + 2 < e->Nr) {
+        // K1(t+2) stays pending on the high-priority stream until B2(t) retires and SMs drain:
+        // its CTAs (which need whole SMs) are then placed before B1(t+1)'s.  (Releasing it by the
+        // end-of-B2 event instead loses that race: 0.320 s against 0.301 s at 8 GPUs.)
+        if (!e->k1_early) JB_CHECK(cudaStreamWaitEvent(e->hstream, e->evB2[t & 1], 0));
+        JB_CHECK(launch_k1(t + 2, e->hstream));
+        JB_CHECK(cudaEventRecord(e->evK[t & 1], e->hstream));
+      } else {
+        JB_CHECK(cudaEventRecord(e->evA, e->hstream));
+      }
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * (t + 1) + 2], e->hstream));
+    }
+    {  // last step: its phase A ran beside B2(Nr-2); B1 takes all that is left, then join
+      const int64_t t = e->Nr - 1;
+      JB_CHECK(cudaStreamWaitEvent(st, e->evB2[(t + 1) & 1], 0));
+      JB_CHECK(cudaStreamWaitEvent(st, e->evA, 0));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 3], st));
+      JB_CHECK(launch_step(t, JB_PHASE_B1, st, grid));
+      if (e->profile)
+        for (int k = 4; k <= 6; ++k) JB_CHECK(cudaEventRecord(e->ev[8 * t + k], st));
+    }
+  } else {
+    JB_CHECK(launch_k1(0, st));
+  }
+  for (int64_t t = 0; t < e->Nr && !la; ++t) {
+    if (e->tc05) {
       // A2 with an EMPTY priority range = scale + broadcast + swap only; then the tcgen05 update of
       // everything, then the fp64 kernel for the swapped-in row (if any)
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], st));
-      JB_CHECK(launch_step(t, JB_PHASE_A2, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t], st));
+      JB_CHECK(launch_step(t, JB_PHASE_A2, st, grid));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 1], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 3], st));
       int rc5 = launch_tc05_b(t, st);
       if (rc5) return rc5;
-      JB_CHECK(launch_step(t, JB_PHASE_B, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 2], st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 3], st));
+      JB_CHECK(launch_step(t, JB_PHASE_B, st, grid));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 4], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 5], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 4], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 6], st));
     } else {
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t], st));
-      JB_CHECK(launch_step(t, JB_PHASE_ALL, st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t], st));
+      JB_CHECK(launch_step(t, JB_PHASE_ALL, st, grid));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 1], st));
       if (e->profile)
-        for (int k = 1; k <= 3; ++k) JB_CHECK(cudaEventRecord(e->ev[6 * t + k], st));
+        for (int k = 3; k <= 5; ++k) JB_CHECK(cudaEventRecord(e->ev[8 * t + k], st));
       if (t + 1 < e->Nr) JB_CHECK(launch_k1(t + 1, st));
-      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * t + 4], st));
+      if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 6], st));
     }
   }
-  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[6 * e->Nr], st));
+  if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * e->Nr], st));
   JB_CHECK(jb_launch_unpermute(e->W, e->rows_loc, e->ldw, e->m, (int)e->Nr, e->stepinfo, st));
   e->launches += (e->rows_loc > 0);
   if (e->profile) {
-    JB_CHECK(cudaEventRecord(e->ev[6 * e->Nr + 1], st));
+    JB_CHECK(cudaEventRecord(e->ev[8 * e->Nr + 1], st));
     JB_CHECK(cudaStreamSynchronize(st));
-    // kernel durations, summed over the steps.  look-ahead: [0] A(t), [1] B1(t), [2] B2(t).
-    // serial: [0] fused step kernel, [2] K1(t+1).  tcgen05: [0] scale/broadcast/swap, [1] update,
-    // [2] K1(t+1).  [3]: look-ahead only, time B2(t) started after B1(t) had been enqueued to start
-    // (> 0: K1(t+1) took longer than B1 did to drain)
+    // kernel durations summed over the steps (event pairs on the stream of each kernel):
+    //   look-ahead: [0] A(t), [1] B1(t), [2] B2(t), [3] K1(t+1) incl. its wait for free SMs
+    //   serial:     [0] fused step kernel, [2] K1(t+1)
+    //   tcgen05:    [0] scale/broadcast/swap, [1] update, [2] K1(t+1)
     for (int k = 0; k < 4; ++k) e->prof_ms[k] = 0;
     for (int64_t t = 0; t < e->Nr; ++t) {
       float x = 0;
-      const bool two = la && t + 1 < e->Nr;
-      JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t], e->ev[6 * t + 1]));
+      JB_CHECK(cudaEventElapsedTime(&x, e->ev[8 * t], e->ev[8 * t + 1]));
       e->prof_ms[0] += x;
-      JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t + 1], e->ev[6 * t + 2]));
+      JB_CHECK(cudaEventElapsedTime(&x, e->ev[8 * t + 3], e->ev[8 * t + 4]));
       e->prof_ms[1] += x;
-      JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t + 3], e->ev[6 * t + 4]));
+      JB_CHECK(cudaEventElapsedTime(&x, e->ev[8 * t + 5], e->ev[8 * t + 6]));
       e->prof_ms[2] += x;
-      if (two) {
-        JB_CHECK(cudaEventElapsedTime(&x, e->ev[6 * t + 2], e->ev[6 * t + 3]));
+      if (la && t + 1 < e->Nr) {
+        JB_CHECK(cudaEventElapsedTime(&x, e->ev[8 * t + 1], e->ev[8 * t + 2]));
         e->prof_ms[3] += x;
       }
     }
     float c = 0;
-    JB_CHECK(cudaEventElapsedTime(&c, e->ev[6 * e->Nr], e->ev[6 * e->Nr + 1]));
+    JB_CHECK(cudaEventElapsedTime(&c, e->ev[8 * e->Nr], e->ev[8 * e->Nr + 1]));
     e->prof_tail_ms = c;
   }
   return JB_OK;

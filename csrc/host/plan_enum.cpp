@@ -10,15 +10,15 @@ extern "C" {
 // nb1 / next_piv_*: look-ahead phases B1 / B2 (next_piv_rank < 0: step t is the last one).
 int64_t jb_plan_enumerate(int32_t m, int32_t p, int32_t rank, int32_t rloc, int64_t ldw, int32_t t,
                           int32_t piv_rank, int32_t piv_slot, int32_t do_swap, int32_t phase,
-                          int32_t pct0, int32_t pct1, int32_t nb1, int32_t next_piv_rank,
-                          int32_t next_piv_slot, int32_t* out, int64_t cap) {
+                          int32_t pct0, int32_t pct1, int32_t nb1, int32_t nearly,
+                          int32_t next_piv_rank, int32_t next_piv_slot, int32_t* out, int64_t cap) {
   StepParams P;
   memset(&P, 0, sizeof(P));
   P.m = m; P.p = p; P.rank = rank; P.t = t; P.rloc = rloc; P.ldw = ldw;
   P.nsub = (m + JB_BM - 1) / JB_BM;
   P.CT = (int)((ldw + JB_BN - 1) / JB_BN);
   P.t_slot = (t % p == rank) ? t / p : -1;
-  P.phase = phase; P.pct0 = pct0; P.pct1 = pct1; P.nb1 = nb1;
+  P.phase = phase; P.pct0 = pct0; P.pct1 = pct1; P.nb1 = nb1; P.nearly = nearly;
   P.has_next = (phase == JB_PHASE_B2 && next_piv_rank >= 0) ? 1 : 0;
   P.sc_t = (phase == JB_PHASE_B2) ? t + 1 : t;
   JbStepInfo si;

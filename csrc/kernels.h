@@ -59,7 +59,11 @@ struct StepParams {
   uint32_t tag;           // swapflag value for this step
   int phase;              // JB_PHASE_*
   int pct0, pct1;         // priority column tiles (cover block column t+1); empty if pct1 < pct0
+  int prev_pct0, prev_pct1;  // phase A: priority range of the previous step; tiles outside it are
+  uint32_t prev_tag;         // B1(t-1)'s early tiles, complete once early[8 + j] >= prev_tag
   int nb1;                // look-ahead: the first nb1 non-priority column tiles belong to phase B1
+  int nearly;             // ... and B1 flags each of its first `nearly` column tiles when complete (<= 8)
+  uint32_t* early;        // local [16]: [0..7] item counters, [8..15] done tags of those tiles
   int has_next;           // phase B2: stepinfo[t + 1] is valid (t + 1 < Nr)
   uint32_t* counter;      // work-item counter of THIS launch (zeroed by the host)
   int only_swapped;       // phase B in tcgen05 mode: only the swapped-in block row stays on the fp64 path

@@ -183,6 +183,13 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;  // tcgen05 mode: the rest is done there
         const int col0 = it.ct * JB_BN;
         if (!kScale || it.type != IT_SCALE) {
+          if (kRowt && P.phase == JB_PHASE_A && (it.ct < P.prev_pct0 || it.ct > P.prev_pct1)) {
+            // phase A runs beside the bulk of the previous step: this tile is one of B1(t-1)'s
+            // early tiles, flagged when every row carries update t-1
+            int j = it.ct - P.prev_pct1 - 1;
+            if (j < 0) j += P.CT;
+            if (j < 8) wait_flag_ge(P.early + 8 + j, P.prev_tag, abort_flag, spin_to);
+          }
           wait_flag_ge(rowflag_local + it.ct, P.row_expect, abort_flag, spin_to);  // pivot-row tile landed
           if (it.type == IT_UPD_SWAPPED)
             for (int c = ctl0; c <= ctl1; ++c) wait_flag_ge(swapflag_local + c * P.nsub + it.sub, P.tag, abort_flag, spin_to);
@@ -192,14 +199,19 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           // UPDP items at the head of the work list (lower claim index, hence running): wait for
           // their flags.  Priority tiles were finished by phase A (an earlier launch on the way to
           // K1(t+1)).  The rest belongs to phase B1, which may still be running beside us but never
-          // waits for this launch: wait until its last CTA has retired.
+          // waits for this launch: its first `nearly` tiles are flagged one by one, for the others
+          // wait until its last CTA has retired.
           const bool pri = pl.npri > 0 && it.ct >= P.pct0 && it.ct <= P.pct1;
-          const int pos = it.ct < P.pct0 ? it.ct : it.ct - pl.npri;
-          if (!pri && pos >= pl.c0) {
-            for (int sb = 0; sb < P.nsub; ++sb)
-              wait_flag_ge(P.prowflag + it.ct * P.nsub + sb, P.tag, abort_flag, spin_to);
-          } else if (!pri && P.b1sync) {
-            wait_flag_ge(P.b1sync + 1, P.tag, abort_flag, spin_to);
+          if (!pri) {
+            const int pos = np_pos(P, pl, it.ct);
+            if (pos >= pl.c0) {
+              for (int sb = 0; sb < P.nsub; ++sb)
+                wait_flag_ge(P.prowflag + it.ct * P.nsub + sb, P.tag, abort_flag, spin_to);
+            } else if (pos < P.nearly) {
+              wait_flag_ge(P.early + 8 + pos, P.tag, abort_flag, spin_to);  // B1 flags these early
+            } else if (P.b1sync) {
+              wait_flag_ge(P.b1sync + 1, P.tag, abort_flag, spin_to);
+            }
           }
           fence_proxy_async();  // other CTAs' generic-proxy stores -> my TMA reads of W
         }
@@ -243,6 +255,12 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
     if (P.only_swapped && it.type != IT_UPD_SWAPPED) continue;
 
     if (kRowt && it.type == IT_ROWT) {
+      if (P.phase == JB_PHASE_A && (it.ct < P.prev_pct0 || it.ct > P.prev_pct1)) {
+        int j = it.ct - P.prev_pct1 - 1;
+        if (j < 0) j += P.CT;
+        if (j < 8 && lane == 0) wait_flag_ge(P.early + 8 + j, P.prev_tag, abort_flag, spin_to);
+        __syncwarp();
+      }
       const int ncol = (int)min((int64_t)JB_BN, P.ldw - col0);  // multiple of 16
       const int64_t roff = (int64_t)(it.sub * JB_BM) * P.ldw + col0;
       rowt_item(P.W + (int64_t)P.t_slot * P.m * P.ldw + roff,
@@ -338,6 +356,17 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         __threadfence();
         named_bar_sync(1, MMA_WARPS * 32);
         if (tid == 0) st_release_sys_u32(P.prowflag + it.ct * P.nsub + it.sub, P.tag);
+      }
+      if (kRowt && !kScale && it.epos >= 0) {  // B1's early column tiles: the last item flags the tile
+        __threadfence();
+        named_bar_sync(1, MMA_WARPS * 32);
+        if (tid == 0) {
+          const uint32_t old = atomicAdd(P.early + it.epos, 1u);
+          if (old == (uint32_t)pl.rtu - 1) {
+            P.early[it.epos] = 0;
+            st_release_sys_u32(P.early + 8 + it.epos, P.tag);
+          }
+        }
       }
     } else if (kScale) {
       // SCALE: column slot t of the pivot row is P^-1 itself; broadcast the tile to all ranks

@@ -23,10 +23,12 @@ struct Item {
   int lrow0;       // first local row of the tile in W (output rows / C rows)
   int rows_valid;  // <= JB_BM
   int prow;        // UPD item of the NEXT pivot row (phase B2): publishes prowflag when stored
+  int epos;        // >= 0: UPD item of B1's early column tile number epos (counted when stored)
 };
 
 struct Plan {
   int nupdp, nscale, nrowt, nupd, nscale2, total;
+  int nupd_a;  // B2: bulk UPD items claimed before the second SCALE group
   int rtu;     // row tiles taking part in UPD of step t on this rank
   int rtu2;    // row tiles of the bulk UPD list of this phase (B2 on the next owner: rtu - nsub)
   int npri;    // priority column tiles (they cover block columns t and t+1)
@@ -45,13 +47,16 @@ struct Plan {
 //   A   : ROWT(t) + UPD(t) of the PRIORITY column tiles: the minimum K1(t+1) needs, so the pivot
 //         search of the next step starts after a short kernel
 //   B1  : ROWT(t) of the other column tiles, UPD(t) of the first nb1 of them; K1(t+1) runs beside
-//         it on a high-priority stream
-//   B2  : launched once K1(t+1) has chosen the next pivot row; may run beside the tail of B1.  On
-//         the owner of that row: UPD(t) of the row's tiles of this phase first (UPDP), then
-//         SCALE(t+1) of the priority tiles and of this phase's tiles straight into all ranks'
-//         pivot-row buffers of step t+1 - the broadcast of step t+1 overlaps the bulk of step t -
-//         then, on every rank, the rest of UPD(t); last, on the owner, SCALE(t+1) of the tiles B1
-//         updates (by then B1 has finished them: no CTA sits waiting for another launch).
+//         it on a high-priority stream.  The non-priority tiles are visited cyclically starting
+//         right behind the priority range, so B1 begins with the tiles of block column t+2 - the
+//         ones phase A of the NEXT step needs; B1 flags each of these `nearly` tiles when done.
+//   B2  : launched once K1(t+1) has chosen the next pivot row; runs beside the tail of B1.  On the
+//         owner of that row: UPD(t) of the row's tiles of this phase first (UPDP); then SCALE(t+1)
+//         straight into all ranks' pivot-row buffers of step t+1 - the broadcast of step t+1
+//         overlaps the bulk of step t - in this order: priority tiles, B1's early tiles (flagged),
+//         this phase's tiles; then, on every rank, the bulk of UPD(t), with the SCALE(t+1) items
+//         of B1's remaining tiles slipped in after the first few bulk items (B1 has retired by
+//         then, so no CTA sits waiting for another launch).
 // tcgen05 mode keeps A2 (SCALE(t) + ROWT(t) of every tile) and B (fp64 update of the swapped-in
 // row only).
 JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo& sn) {
@@ -66,6 +71,7 @@ JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo
   const bool owner = (si.piv_rank == P.rank);
   const bool has_t = (P.t_slot >= 0);
   pl.nupdp = pl.nscale = pl.nrowt = pl.nscale2 = 0;
+  pl.nupd_a = 0;
   pl.c0 = 0;
   pl.c1 = 0;
   int ucols = 0;  // column tiles of the bulk UPD list
@@ -94,9 +100,10 @@ JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo
     pl.c1 = pl.nnp;
     ucols = pl.c1 - pl.c0;
     if (P.has_next && sn.piv_rank == P.rank) {
+      const int ne = P.nearly < pl.c0 ? P.nearly : pl.c0;
       pl.nupdp = P.nsub * ucols;
-      pl.nscale = P.nsub * (pl.npri + ucols);
-      pl.nscale2 = P.nsub * pl.c0;
+      pl.nscale = P.nsub * (pl.npri + ne + ucols);
+      pl.nscale2 = P.nsub * (pl.c0 - ne);
       pl.rtu2 = pl.rtu - P.nsub;
       // two slots are left out of the bulk list: block row t (ROWT) and the next pivot row (UPDP)
       if (pl.skip_a < 0 || sn.piv_slot < pl.skip_a) {
@@ -112,13 +119,25 @@ JB_HD Plan make_plan(const StepParams& P, const JbStepInfo& si, const JbStepInfo
     }
   }
   pl.nupd = pl.rtu2 * ucols;
+  if (pl.nscale2 > 0) {  // about 1/8 of the bulk, whole column tiles
+    const int cols_a = (ucols + 7) / 8;
+    pl.nupd_a = pl.rtu2 * cols_a;
+  }
   pl.total = pl.nupdp + pl.nscale + pl.nrowt + pl.nupd + pl.nscale2;
   return pl;
 }
 
-// position among the non-priority column tiles -> column tile
+// position among the non-priority column tiles -> column tile: cyclic, starting right behind the
+// priority range (block column t+2 first)
 JB_HD int np_ct(const StepParams& P, const Plan& pl, int pos) {
-  return (pl.npri == 0 || pos < P.pct0) ? pos : pos + pl.npri;
+  if (pl.npri == 0) return pos;
+  const int ct = P.pct1 + 1 + pos;
+  return ct < P.CT ? ct : ct - P.CT;
+}
+// ... and back (ct must not be a priority tile)
+JB_HD int np_pos(const StepParams& P, const Plan& pl, int ct) {
+  if (pl.npri == 0) return ct;
+  return ct > P.pct1 ? ct - P.pct1 - 1 : ct + P.CT - P.pct1 - 1;
 }
 
 JB_HD int upd_type(const StepParams& P, const JbStepInfo& si, int slot) {
@@ -129,6 +148,7 @@ JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const JbStepInfo& s
                   int idx) {
   Item it;
   it.prow = 0;
+  it.epos = -1;
   const int ph = P.phase;
   if (idx < pl.nupdp) {  // B2: the next pivot row first
     const int pos = idx / P.nsub;
@@ -142,17 +162,25 @@ JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const JbStepInfo& s
     const int k = idx - pl.nupdp;
     const int pos = k / P.nsub;
     it.sub = k - pos * P.nsub;
-    if (ph == JB_PHASE_B2)  // priority tiles first (phase A of the next step needs them), then ours
-      it.ct = pos < pl.npri ? P.pct0 + pos : np_ct(P, pl, pl.c0 + pos - pl.npri);
-    else
+    if (ph == JB_PHASE_B2) {
+      // priority tiles, then B1's early tiles (both needed by phase A of the next step), then ours
+      const int ne = P.nearly < pl.c0 ? P.nearly : pl.c0;
+      if (pos < pl.npri) it.ct = P.pct0 + pos;
+      else if (pos < pl.npri + ne) it.ct = np_ct(P, pl, pos - pl.npri);
+      else it.ct = np_ct(P, pl, pl.c0 + pos - pl.npri - ne);
+    } else {
       it.ct = (ph == JB_PHASE_A2) ? np_ct(P, pl, pos) : pos;
+    }
     it.lrow0 = it.sub * JB_BM;  // row inside the pivot-row buffer
-  } else if (idx >= pl.total - pl.nscale2) {  // B2: SCALE(t+1) of the tiles phase B1 updates
+  } else if (pl.nscale2 > 0 && idx >= pl.nupdp + pl.nscale + pl.nupd_a &&
+             idx < pl.nupdp + pl.nscale + pl.nupd_a + pl.nscale2) {
+    // B2: SCALE(t+1) of the tiles phase B1 updates (behind its early tiles)
     it.type = IT_SCALE;
-    const int k = idx - (pl.total - pl.nscale2);
+    const int k = idx - (pl.nupdp + pl.nscale + pl.nupd_a);
     const int pos = k / P.nsub;
     it.sub = k - pos * P.nsub;
-    it.ct = np_ct(P, pl, pos);
+    const int ne = P.nearly < pl.c0 ? P.nearly : pl.c0;
+    it.ct = np_ct(P, pl, ne + pos);
     it.lrow0 = it.sub * JB_BM;
   } else if (idx < pl.nupdp + pl.nscale + pl.nrowt) {
     it.type = IT_ROWT;
@@ -162,7 +190,8 @@ JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const JbStepInfo& s
     it.ct = (ph == JB_PHASE_A) ? P.pct0 + pos : np_ct(P, pl, pos);
     it.lrow0 = P.t_slot * P.m + it.sub * JB_BM;
   } else {
-    const int u = idx - pl.nupdp - pl.nscale - pl.nrowt;
+    int u = idx - pl.nupdp - pl.nscale - pl.nrowt;
+    if (pl.nscale2 > 0 && u >= pl.nupd_a) u -= pl.nscale2;  // B2: second part of the bulk
     const int cpos = u / pl.rtu2;
     const int rt = u - cpos * pl.rtu2;
     it.ct = (ph == JB_PHASE_A) ? P.pct0 + cpos : np_ct(P, pl, pl.c0 + cpos);
@@ -172,6 +201,7 @@ JB_HD Item decode(const StepParams& P, const JbStepInfo& si, const JbStepInfo& s
     if (pl.skip_b >= 0 && slot >= pl.skip_b) slot += 1;
     it.lrow0 = slot * P.m + it.sub * JB_BM;
     it.type = upd_type(P, si, slot);
+    if (ph == JB_PHASE_B1 && cpos < P.nearly) it.epos = cpos;
   }
   it.rows_valid = ((P.m - it.sub * JB_BM) < JB_BM ? (P.m - it.sub * JB_BM) : JB_BM);
   return it;

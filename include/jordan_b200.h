@@ -63,11 +63,12 @@ double jb_cpu_residual(const double* a, const double* x, int64_t n);
 /* Work list of the fused step kernel for one phase (CPU-side view of csrc/step_plan.h, used by the
  * scheduling-invariant tests).  out[5*i..] = {type, column tile, first local row, rows, item
  * belongs to the NEXT pivot row}.  phase: 0 ALL, 1 A, 2 B, 3 A2, 4 S, 5 B1, 6 B2; nb1 = number of
- * non-priority column tiles of phase B1; next_piv_* = pivot of step t+1 (rank < 0: none). */
+ * non-priority column tiles of phase B1, the first `nearly` of them flagged early; next_piv_* =
+ * pivot of step t+1 (rank < 0: none). */
 int64_t jb_plan_enumerate(int32_t m, int32_t p, int32_t rank, int32_t rloc, int64_t ldw, int32_t t,
                           int32_t piv_rank, int32_t piv_slot, int32_t do_swap, int32_t phase,
-                          int32_t pct0, int32_t pct1, int32_t nb1, int32_t next_piv_rank,
-                          int32_t next_piv_slot, int32_t* out, int64_t cap);
+                          int32_t pct0, int32_t pct1, int32_t nb1, int32_t nearly,
+                          int32_t next_piv_rank, int32_t next_piv_slot, int32_t* out, int64_t cap);
 
 /* ------------------------------------------------------------------ GPU engine (libjordan_b200) */
 typedef struct JbEngine JbEngine;
@@ -115,10 +116,11 @@ int jb_engine_pivots(JbEngine* e, int32_t* piv_out /* Nr */);
 int64_t jb_engine_launch_count(const JbEngine* e); /* kernels launched by this engine so far */
 /* per-kernel CUDA-event timing of the last jb_engine_invert (adds a stream sync; off by default) */
 int jb_engine_set_profiling(JbEngine* e, int on);
-/* seg_ms[4], kernel durations summed over the steps.  Look-ahead schedule: [0] phase A (swap +
- * block columns t, t+1), [1] phase B1 (K1(t+1) runs beside it), [2] phase B2 (next pivot row scaled
- * + broadcast, rest of the update), [3] start of B2 minus end of B1 (negative: they overlapped).
- * Serial schedule: [0] fused step kernel, [2] K1(t+1).  tail_ms: final column un-permutation. */
+/* seg_ms[4], kernel durations summed over the steps (the kernels of the look-ahead schedule
+ * overlap, so they do not add up to the inversion time).  Look-ahead: [0] phase A (swap + block
+ * columns t, t+1), [1] phase B1 (K1(t+1) runs beside it), [2] phase B2 (next pivot row scaled +
+ * broadcast, rest of the update), [3] K1(t+1) including its wait for free SMs.  Serial schedule:
+ * [0] fused step kernel, [2] K1(t+1).  tail_ms: final column un-permutation. */
 int jb_engine_phase_times(JbEngine* e, double* seg_ms, double* tail_ms);
 
 /* results */

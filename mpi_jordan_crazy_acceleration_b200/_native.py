@@ -66,7 +66,7 @@ def _declare_host(lib) -> None:
         "jb_cpu_inverse_block": (C.c_int, [C.c_void_p, C.c_void_p, dbl, i64]),
         "jb_cpu_minloc_fold": (C.c_int, [C.c_void_p, C.c_void_p, i64]),
         "jb_cpu_residual": (dbl, [C.c_void_p, C.c_void_p, i64]),
-        "jb_plan_enumerate": (i64, [i32, i32, i32, i32, i64, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32,
+        "jb_plan_enumerate": (i64, [i32, i32, i32, i32, i64, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32,
                                     C.c_void_p, i64]),
     }
     for name, (res, args) in sig.items():

@@ -303,10 +303,10 @@ class JordanSolver:
         if self.precision == "tc05":
             return {"scale_swap_ms": seg[0], "tc05_update_ms": seg[1], "k1_ms": seg[2], "tail_ms": tail.value,
                     "lookahead": False}
-        # look-ahead: kernel durations of A(t) (swap + block columns t, t+1), B1(t) (K1(t+1) beside
-        # it), B2(t) (next pivot row scaled + broadcast, rest of the update; it moves in while B1
-        # drains), and how long after the end of B1 the first B2 CTA started (negative = overlap)
-        return {"stepA_ms": seg[0], "stepB1_ms": seg[1], "stepB2_ms": seg[2], "b2_start_after_b1_end_ms": seg[3],
+        # look-ahead: kernel durations (they overlap, so they do not add up to the inversion time) of
+        # A(t) (swap + block columns t, t+1; beside B2(t-1)), B1(t), B2(t) (next pivot row scaled +
+        # broadcast, rest of the update; moves in while B1 drains) and K1(t+1) incl. its wait for SMs
+        return {"stepA_ms": seg[0], "stepB1_ms": seg[1], "stepB2_ms": seg[2], "k1_ms": seg[3],
                 "tail_ms": tail.value, "lookahead": True}
 
     @property

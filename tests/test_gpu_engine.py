@@ -187,10 +187,14 @@ def test_lookahead_schedule_is_bitwise_equal_to_serial(fid, n, m):
     300 candidate CTAs), where K1(t+1) runs in several waves beside the update and any read of a
     buffer K1 overwrites (the inverse of the chosen pivot block, the L panel) would show up here."""
     Xs, ps, rs = _invert_w(n, m, fid, {"JB_NO_LOOKAHEAD": "1"})
-    for frac in ("0.4", "0.0", "1.0"):
-        Xl, pl, rl = _invert_w(n, m, fid, {"JB_B1_FRAC": frac})
-        assert pl == ps
-        assert torch.equal(Xl, Xs), float((Xl - Xs).abs().max())
+    # JB_SCHED: 1 = phase A in line, 2 = phase A beside B2 of the previous step; JB_B1_FRAC: share of
+    # the tiles updated while K1 runs (0 and 1 are the degenerate splits)
+    for env in ({"JB_SCHED": "1"}, {"JB_SCHED": "2"}, {"JB_SCHED": "2", "JB_B1_FRAC": "0.0"},
+                {"JB_SCHED": "1", "JB_B1_FRAC": "1.0"}, {"JB_SCHED": "2", "JB_B1_FRAC": "1.0"},
+                {"JB_SCHED": "2", "JB_K1_GATED": "1"}, {"JB_SCHED": "1", "JB_B2_SERIAL": "1"}):
+        Xl, pl, rl = _invert_w(n, m, fid, env)
+        assert pl == ps, env
+        assert torch.equal(Xl, Xs), (env, float((Xl - Xs).abs().max()))
         assert abs(rl - rs) <= 1e-9 * rs   # row sums are accumulated with atomics: last-bit noise
     if fid == 6:
         assert any(g != t for t, g in enumerate(ps))   # block-row swaps did happen

@@ -14,8 +14,9 @@ B2(t-1), or by the S prologue for t = 0).
     - a swapped-in row additionally needs the ROWT pushes of its own column tile and of the tiles
       that hold block column t (this dependency once dead-locked when those pushes lived in a
       later phase);
-    - SCALE(t+1) of a column tile needs UPD(t) of the next pivot row on that tile: phase A / B1
-      (earlier launches) or the UPDP items at the head of B2 (lower claim index);
+    - SCALE(t+1) of a column tile needs UPD(t) of the next pivot row on that tile: phase A (an
+      earlier launch), phase B1 (launched earlier, possibly still running beside B2, never waiting
+      for it) or the UPDP items at the head of B2 (lower claim index);
 * the pivot-row buffer of parity (t+1)&1 that SCALE(t+1) overwrites is no longer read by step t-1
   (its readers are the phases of step t-1, all launched before K1(t+1), whose cross-rank min-loc
   every rank's B2(t) waits for): checked here as "SCALE(t+1) lives in B2(t), never earlier".
@@ -34,11 +35,11 @@ BM, BN = 64, 128
 
 
 def enumerate_items(m, p, rank, rloc, ldw, t, piv_rank, piv_slot, do_swap, phase, pct0, pct1, nb1=0,
-                    next_rank=-1, next_slot=0):
+                    next_rank=-1, next_slot=0, nearly=0):
     cap = 1 << 20
     buf = (C.c_int32 * (5 * cap))()
     n = _native.host().jb_plan_enumerate(m, p, rank, rloc, ldw, t, piv_rank, piv_slot, do_swap, phase, pct0, pct1,
-                                         nb1, next_rank, next_slot, buf, cap)
+                                         nb1, nearly, next_rank, next_slot, buf, cap)
     assert n >= 0
     return [tuple(buf[5 * i + k] for k in range(5)) for i in range(n)]
 
@@ -68,7 +69,9 @@ def test_phases_cover_everything_once_and_never_wait_forward(n, m, p, t, piv_g, 
     nxt_rank, nxt_slot = nxt_g % p, nxt_g // p
     pct0, pct1 = engine_priority(t, m, CT)
     nnp = CT - (pct1 - pct0 + 1)
-    nb1 = min(nnp, int(frac * nnp + 0.999))
+    nearly = max(0, min(nnp, 8, engine_priority(t + 1, m, CT)[1] - pct1))   # mirrors launch_step()
+    nb1 = min(nnp, max(nearly, int(frac * nnp + 0.999)))
+    pri_next = set(range(*[(a, b + 1) for a, b in [engine_priority(t + 1, m, CT)]][0]))
     t_rank = t % p
     tcols = set(range((t * m) // BN, ((t + 1) * m - 1) // BN + 1))   # tiles holding block column t
 
@@ -79,7 +82,7 @@ def test_phases_cover_everything_once_and_never_wait_forward(n, m, p, t, piv_g, 
         items = {}
         for ph in (A, B1, B2):
             items[ph] = enumerate_items(m, p, rank, rloc, ldw, t, piv_rank, piv_slot, do_swap, ph, pct0, pct1,
-                                        nb1, nxt_rank, nxt_slot)
+                                        nb1, nxt_rank, nxt_slot, nearly)
             for idx, (ty, ct, lrow0, rows, prow) in enumerate(items[ph]):
                 sub = (lrow0 % m) // BM if ty != SCALE else lrow0 // BM
                 if ty == SCALE:
@@ -115,6 +118,16 @@ def test_phases_cover_everything_once_and_never_wait_forward(n, m, p, t, piv_g, 
     full = {(sub, ct) for sub in range(nsub) for ct in range(CT)}
     assert set(rowt_at) == full
     assert set(scale_next_at) == full
+    # the tiles phase A of step t+1 needs are scaled first, and none of them waits for the whole of
+    # B1: they are priority tiles of step t (finished by A(t)) or B1's flagged early tiles
+    first = sorted(scale_next_at.items(), key=lambda kv: kv[1])[:nsub * (pct1 - pct0 + 1 + nearly)]
+    assert pri_next <= {ct for (_, ct), _ in first}
+    b1_order = []
+    for ty, ct, *_ in per_rank[nxt_rank][B1]:
+        if ty in (UPD, UPD_SW) and ct not in b1_order:
+            b1_order.append(ct)
+    for ct in pri_next - set(range(pct0, pct1 + 1)):
+        assert ct in b1_order[:nearly], (ct, b1_order[:4], nearly)
 
     def available(dep, where_rank, me_rank, me):
         """dep = (phase order, idx) of a producer on rank `where_rank`; me likewise on me_rank."""
