@@ -40,6 +40,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-alt", action="store_true", help="skip the tcgen05 second arm")
     ap.add_argument("--residual", action="store_true", help="also compute ||AX-I|| after the timed region")
+    ap.add_argument("--no-checks", action="store_true",
+                    help="skip ref_config_check / pivoting_check (run after the timed region)")
     return ap.parse_args()
 
 
@@ -167,6 +169,9 @@ def run_own(args) -> dict:
     if residual is not None:
         out["residual"] = residual
     s.close()
+    if not args.no_checks:
+        out["ref_config_check"] = ref_config_check(args, comm, local_rank)
+        out["pivoting_check"] = pivoting_check(args, comm, local_rank)
     # ---------------------------------------------------------------- second arm: tcgen05 update path
     # Same inversion with the trailing update on tcgen05.mma kind::i8 (error-free int8 split, exact
     # int32 accumulation in TMEM).  Reported next to the headline, never instead of it: the headline
@@ -196,6 +201,84 @@ def run_own(args) -> dict:
             pass
         s2.close()
     return out if comm.rank == 0 else {}
+
+
+def ref_config_check(args, comm, local_rank) -> list:
+    """The reference arm (`--impl reference`) cannot finish the headline n on host CPUs in bench
+    time and measures at the largest halved n that fits its budget (baseline/ref_cpu/
+    run_reference.py).  Whatever n it picks, this list holds the own engine at exactly that n and
+    the same m, so a like-for-like ratio can be read from the two records: device-timed
+    elimination, and end to end (pinned host rows -> device, inversion, verdict + corner back)."""
+    import torch
+
+    from mpi_jordan_crazy_acceleration_b200.models.eager import formula_rows
+    from mpi_jordan_crazy_acceleration_b200.models.jordan import JordanSolver
+
+    rows_out = []
+    n = args.n // 2
+    while n >= max(1024, args.m):
+        s = JordanSolver(n, args.m, comm=comm, device=local_rank, precision=args.precision)
+        lay = s.layout
+        for _ in range(2):
+            s.fill_formula(args.formula)
+            sec = s.invert()
+        gl = torch.tensor(lay.global_rows(), dtype=torch.int64)
+        host = formula_rows(args.formula, n, gl).pin_memory() if lay.rows_real else \
+            torch.empty(0, n, dtype=torch.float64)
+
+        def e2e_step():
+            s.upload_local_rows(host)
+            s.invert_async()
+            s.status()
+            return s.corner("X")
+
+        e2e_step()
+        torch.cuda.synchronize()
+        comm.barrier()
+        t0 = time.perf_counter()
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        comm.barrier()
+        e2e_sec = comm.allreduce_max((time.perf_counter() - t0) / 2)
+        rows_out.append({"n": n, "m": args.m, "seconds": sec, "value": flops(n) / sec / 1e9,
+                         "e2e_seconds": e2e_sec, "e2e_value": flops(n) / e2e_sec / 1e9, "unit": "GFLOP/s"})
+        s.close()
+        n //= 2
+    return rows_out
+
+
+def pivoting_check(args, comm, local_rank) -> dict:
+    """Cross-GPU correctness where the driver sees it: the headline generator |i-j| always pivots on
+    the diagonal, so the block-row swap path (peer stores into the pivot owner's swap buffer, swapped
+    -in row update) never runs in the timed region.  Formula 6 (rows rotated by n/2) needs a swap in
+    the first Nr/2 steps; n is chosen so that the two rows of a swap live on different ranks for 2,
+    4 and 8 GPUs.  Compared against the CPU oracle (intended semantics of main.cpp:1026-1194)."""
+    import torch
+
+    from mpi_jordan_crazy_acceleration_b200.models.eager import formula_rows
+    from mpi_jordan_crazy_acceleration_b200.models.jordan import JordanSolver
+    from mpi_jordan_crazy_acceleration_b200.ops import cpu_block_jordan
+
+    m = 128
+    n = 18 * m
+    s = JordanSolver(n, m, comm=comm, device=local_rank)
+    s.fill_formula(6)
+    s.invert()
+    piv = s.pivots()
+    X = s.gather_inverse()
+    res = s.residual()
+    s.close()
+    out = {}
+    if comm.rank == 0:
+        A = formula_rows(6, n, torch.arange(n))
+        Xo, pivo = cpu_block_jordan(A, m, comm.world)
+        swaps = [(t, g) for t, g in enumerate(pivo) if g != t]
+        out = {"formula": 6, "n": n, "m": m, "pivots_match_oracle": piv == pivo, "swaps": len(swaps),
+               "cross_gpu_swaps": sum(1 for t, g in swaps if t % comm.world != g % comm.world),
+               "maxerr": float((X - Xo).abs().max() / Xo.abs().max()), "residual": res}
+    comm.barrier()
+    return out
 
 
 def run_baseline(args) -> dict:
