@@ -17,6 +17,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include <string>
 #include <vector>
@@ -47,46 +48,159 @@ static void print_corner(JbEngine* e, int which, int64_t n, int m, int nm) {
   (void)n;
 }
 
+// Symmetric region of the engine.  Default: the native VMM heap (cuMemCreate + POSIX descriptors
+// passed over the MPI shim's sockets + NVLS multicast object, csrc/comm/symm_heap.cpp).  JB_SYMM=ipc
+// (or a build against an MPI without a descriptor channel) selects cudaMalloc + cudaIpc handles,
+// unicast only.  Every decision is voted on so that all ranks take the same path.
+static JbSymmHeap* g_heap = nullptr;
+static const char* g_symm_mode = "local";
+
+static int vote_min(int v) {
+  int out = v;
+  MPI_Allreduce(&v, &out, 1, MPI_INT, MPI_MIN, MPI_COMM_WORLD);
+  return out;
+}
+
+static int setup_symm_ipc(JbEngine* e) {
+  int rc = jb_engine_alloc_symm(e);
+  if (vote_min(rc) != JB_OK) return rc ? rc : JB_ERR_NOMEM;
+  char mine[64];
+  std::vector<char> all((size_t)64 * g_size);
+  if ((rc = jb_engine_ipc_handle(e, 0, mine)) != JB_OK) return rc;
+  MPI_Allgather(mine, 64, MPI_BYTE, all.data(), 64, MPI_BYTE, MPI_COMM_WORLD);
+  if ((rc = jb_engine_open_peers(e, 0, all.data())) != JB_OK) return rc;
+  g_symm_mode = "cuda-ipc";
+  return JB_OK;
+}
+
+static int setup_symm(JbEngine* e, int device) {
+  if (g_size == 1) return jb_engine_alloc_symm(e);
+  const char* mode = getenv("JB_SYMM");
+#ifndef JB_MPI_SHIM_HAS_FD_PASSING
+  mode = "ipc";
+#endif
+  if (mode && !strcmp(mode, "ipc")) return setup_symm_ipc(e);
+#ifdef JB_MPI_SHIM_HAS_FD_PASSING
+  int fd = -1;
+  int rc = jb_symm_heap_create(jb_engine_symm_bytes(e), device, g_rank, g_size, getenv("JB_NO_MULTICAST") ? 0 : 1,
+                               &g_heap, &fd);
+  if (vote_min(rc) != JB_OK) {  // no VMM / descriptors on some rank: every rank falls back together
+    if (g_heap) jb_symm_heap_destroy(g_heap);
+    g_heap = nullptr;
+    if (fd >= 0) close(fd);
+    if (g_rank == 0 && getenv("JB_VERBOSE")) printf("symmetric heap: VMM path unavailable, using cudaIpc\n");
+    return setup_symm_ipc(e);
+  }
+  std::vector<int> fds((size_t)g_size, -1);
+  for (int r = 0; r < g_size; ++r)
+    if (r != g_rank) jb_mpi_send_fd(fd, r);
+  for (int r = 0; r < g_size; ++r)
+    if (r != g_rank) fds[r] = jb_mpi_recv_fd(r);
+  close(fd);
+  rc = jb_symm_heap_import(g_heap, fds.data());
+  if (vote_min(rc) != JB_OK) return rc ? rc : JB_ERR_CUDA;
+  // NVLS multicast alias: all ranks must succeed at every stage, else everybody drops it
+  int mc = vote_min(jb_symm_heap_multicast_supported(g_heap));
+  if (mc) {
+    int ok = 1;
+    if (g_rank == 0) {
+      int mfd = -1;
+      ok = jb_symm_heap_mc_create(g_heap, &mfd) == JB_OK;
+      for (int r = 1; r < g_size; ++r) {
+        MPI_Send(&ok, 1, MPI_INT, r, 3, MPI_COMM_WORLD);
+        if (ok) jb_mpi_send_fd(mfd, r);
+      }
+      if (mfd >= 0) close(mfd);
+    } else {
+      MPI_Recv(&ok, 1, MPI_INT, 0, 3, MPI_COMM_WORLD, MPI_STATUS_IGNORE);
+      if (ok) ok = jb_symm_heap_mc_import(g_heap, jb_mpi_recv_fd(0)) == JB_OK;
+    }
+    ok = vote_min(ok);
+    if (ok) ok = vote_min(jb_symm_heap_mc_add(g_heap) == JB_OK);     // vote = barrier: all devices added
+    if (ok) ok = vote_min(jb_symm_heap_mc_bind(g_heap) == JB_OK);    // vote = barrier: all bound
+    if (!ok) {
+      if (getenv("JB_VERBOSE")) fprintf(stderr, "[rank %d] multicast set-up failed: %s\n", g_rank, jb_last_error());
+      jb_symm_heap_mc_drop(g_heap);
+    }
+    mc = ok;
+  }
+  std::vector<void*> ptrs((size_t)g_size);
+  for (int r = 0; r < g_size; ++r) ptrs[r] = jb_symm_heap_ptr(g_heap, r);
+  rc = jb_engine_bind_symm(e, ptrs.data(), mc ? jb_symm_heap_mc_ptr(g_heap) : nullptr);
+  g_symm_mode = mc ? "vmm+nvls" : "vmm";
+  return rc;
+#else
+  (void)device;
+  return JB_ERR_ARG;
+#endif
+}
+
 static int solve(int64_t n, int m, int print_size, int formula, const char* name) {
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     if (g_rank == 0) printf("no CUDA device\n");
     return -1;
   }
+  // the reference accepts any m, including m > n (one block row of height n, main.cpp:124-127)
+  if ((int64_t)m > n) m = (int)n;
   JbConfig cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.n = n; cfg.m = m; cfg.p = g_size; cfg.rank = g_rank; cfg.device = g_rank % ndev;
   cfg.keep_copy = name ? 1 : 0;
+  if (const char* pr = getenv("JB_PRECISION")) cfg.precision = !strcmp(pr, "tc05") ? 1 : 0;
   JbEngine* e = nullptr;
-  int loc_err = jb_engine_create(&cfg, &e) != JB_OK ? 1 : 0, glob_err = 0;
-  if (!loc_err) loc_err = jb_engine_alloc_symm(e) != JB_OK ? 1 : 0;
-  MPI_Allreduce(&loc_err, &glob_err, 1, MPI_INT, MPI_SUM, MPI_COMM_WORLD);  // C2, main.cpp:371
-  if (glob_err) {
-    if (g_rank == 0) printf("Not enough memory!\n");
-    if (loc_err && getenv("JB_VERBOSE")) fprintf(stderr, "[rank %d] %s\n", g_rank, jb_last_error());
+  int rc_create = jb_engine_create(&cfg, &e);
+  std::string create_msg = rc_create != JB_OK ? jb_last_error() : "";
+  int worst = vote_min(rc_create);  // C2, main.cpp:371: every rank learns the most severe code
+  if (worst == JB_OK) {
+    rc_create = setup_symm(e, cfg.device);
+    if (rc_create != JB_OK) create_msg = jb_last_error();
+    worst = vote_min(rc_create);
+  }
+  if (worst != JB_OK) {
+    if (g_rank == 0) {
+      if (worst == JB_ERR_NOMEM) printf("Not enough memory!\n");  // main.cpp:375
+      else if (worst == JB_ERR_ARG) printf("unsupported configuration: %s\n", create_msg.empty() ? "rejected by another rank" : create_msg.c_str());
+      else printf("cannot set up the GPUs: %s\n", create_msg.empty() ? "failure on another rank" : create_msg.c_str());
+    }
+    if (rc_create != JB_OK && getenv("JB_VERBOSE")) fprintf(stderr, "[rank %d] %s\n", g_rank, create_msg.c_str());
     if (e) jb_engine_destroy(e);
+    if (g_heap) jb_symm_heap_destroy(g_heap);
     return -1;
   }
-  if (g_size > 1) {
-    for (int which = 0; which < 2; ++which) {
-      char mine[64];
-      std::vector<char> all((size_t)64 * g_size);
-      if (jb_engine_ipc_handle(e, which, mine) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
-      MPI_Allgather(mine, 64, MPI_BYTE, all.data(), 64, MPI_BYTE, MPI_COMM_WORLD);
-      if (jb_engine_open_peers(e, which, all.data()) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
-    }
+  if (g_size > 1) {  // matrix slabs: peer-readable for the residual's direct X pulls (C13)
+    char mine[64];
+    std::vector<char> all((size_t)64 * g_size);
+    if (jb_engine_ipc_handle(e, 1, mine) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
+    MPI_Allgather(mine, 64, MPI_BYTE, all.data(), 64, MPI_BYTE, MPI_COMM_WORLD);
+    if (jb_engine_open_peers(e, 1, all.data()) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
     MPI_Barrier(MPI_COMM_WORLD);
   }
+  if (g_rank == 0 && getenv("JB_VERBOSE")) printf("symmetric region: %s\n", g_symm_mode);
 
-  // ---- matrix: text file scattered block row by block row (read_matrix, C3/C4) or generator
+  // ---- matrix: text file scattered block row by block row (read_matrix, C3/C4) or generator.
+  //      Rank 0 scans the file once and holds ONE block row at a time (main.cpp:249-263).
   if (name) {
     int err = 0;
-    std::vector<double> full;
-    if (g_rank == 0) {
-      full.resize((size_t)n * n);
-      err = jb_read_matrix_full(name, n, full.data());
+    JbMatrixReader* rd = nullptr;
+    if (g_rank == 0) err = jb_matrix_reader_open(name, &rd);
+    MPI_Bcast(&err, 1, MPI_INT, 0, MPI_COMM_WORLD);  // main.cpp:237
+    const int64_t Nr = jb_num_block_rows(n, m);
+    std::vector<double> buf((size_t)m * n);
+    for (int64_t I = 0; I < Nr && !err; ++I) {
+      const int owner = (int)(I % g_size);
+      const int64_t h = (I == Nr - 1) ? n - I * m : m;
+      if (g_rank == 0) err = jb_matrix_reader_next(rd, h * n, buf.data());
+      MPI_Bcast(&err, 1, MPI_INT, 0, MPI_COMM_WORLD);  // fail fast, main.cpp:277
+      if (err) break;
+      if (g_rank == 0 && owner != 0) MPI_Send(buf.data(), (int)(h * n), MPI_DOUBLE, owner, 0, MPI_COMM_WORLD);
+      if (g_rank == owner) {
+        if (owner != 0) MPI_Recv(buf.data(), (int)(h * n), MPI_DOUBLE, 0, 0, MPI_COMM_WORLD, MPI_STATUS_IGNORE);
+        if (jb_engine_upload_rows(e, buf.data(), (I / g_size) * m, h, nullptr) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
+        cudaStreamSynchronize(nullptr);  // buf is reused for the next block row
+      }
     }
-    MPI_Bcast(&err, 1, MPI_INT, 0, MPI_COMM_WORLD);
+    if (rd) jb_matrix_reader_close(rd);
     if (err) {
       if (g_rank == 0) {
         if (err == -1) printf("cannot open %s\n", name);
@@ -94,26 +208,8 @@ static int solve(int64_t n, int m, int print_size, int formula, const char* name
         else printf("unknown error %d in %s\n", err, name);
       }
       jb_engine_destroy(e);
+      if (g_heap) jb_symm_heap_destroy(g_heap);
       return -2;
-    }
-    const int64_t Nr = jb_num_block_rows(n, m);
-    std::vector<double> buf((size_t)m * n);
-    for (int64_t I = 0; I < Nr; ++I) {
-      const int owner = (int)(I % g_size);
-      const int64_t h = (I == Nr - 1) ? n - I * m : m;
-      const double* src = nullptr;
-      if (g_rank == 0) {
-        src = full.data() + (size_t)I * m * n;
-        if (owner != 0) MPI_Send((void*)src, (int)(h * n), MPI_DOUBLE, owner, 0, MPI_COMM_WORLD);
-      }
-      if (g_rank == owner) {
-        if (owner != 0) {
-          MPI_Recv(buf.data(), (int)(h * n), MPI_DOUBLE, 0, 0, MPI_COMM_WORLD, MPI_STATUS_IGNORE);
-          src = buf.data();
-        }
-        if (jb_engine_upload_rows(e, src, (I / g_size) * m, h, nullptr) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
-        cudaStreamSynchronize(nullptr);
-      }
     }
     if (jb_engine_finish_upload(e, nullptr) != JB_OK) { fprintf(stderr, "%s\n", jb_last_error()); MPI_Abort(MPI_COMM_WORLD, 2); }
   } else {
@@ -144,9 +240,11 @@ static int solve(int64_t n, int m, int print_size, int formula, const char* name
     if (g_rank == 0) {
       if (rc_min == JB_ERR_NOMEM) printf("not enough memory for block\n");
       else if (rc_min == JB_ERR_SINGULAR) printf("singular matrix\n");
+      else if (rc_min == JB_ERR_TIMEOUT) printf("a rank stopped responding (cross-GPU wait timed out)\n");
       else printf("unknown error: %d\n", rc_min);
     }
     jb_engine_destroy(e);
+    if (g_heap) jb_symm_heap_destroy(g_heap);
     return -1;
   }
   float ms = 0;
@@ -176,6 +274,7 @@ static int solve(int64_t n, int m, int print_size, int formula, const char* name
   }
   MPI_Barrier(MPI_COMM_WORLD);
   jb_engine_destroy(e);
+  if (g_heap) jb_symm_heap_destroy(g_heap);
   return 0;
 }
 

@@ -104,7 +104,7 @@ struct JbEngine {
   JbStepInfo* stepinfo = nullptr;
   double *Xp = nullptr, *rowsum = nullptr, *scratch_max = nullptr, *Rslab = nullptr;
   // symmetric region
-  size_t off_rowbuf[2], off_swapbuf[2], off_rowflag[2], off_swapflag[2], off_mail, symm_bytes;
+  size_t off_rowbuf[2], off_swapbuf[2], off_rowflag[2], off_swapflag[2], off_mail, off_stepdone, symm_bytes;
   uint32_t* prowflag = nullptr;  // [CT][nsub] local flags of the pivot-row look-ahead (phase B2)
   double b1_frac = -1.0;         // share of the non-priority column tiles given to phase B1 (<0: auto)
   unsigned char* symm_peers[JB_MAX_RANKS] = {nullptr};
@@ -252,6 +252,7 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   e->off_swapflag[0] = off; off += sfb;
   e->off_swapflag[1] = off; off += sfb;
   e->off_mail = off; off += align_up(2 * JB_MAX_RANKS * sizeof(JbMail), 256);
+  e->off_stepdone = off; off += align_up(JB_MAX_RANKS * 4, 256);
   e->symm_bytes = align_up(off, 4096);
   e->W_peers[e->rank] = e->W;
   {  // watchdog for cross-GPU spin-waits: default 30 s, JB_SPIN_TIMEOUT_MS=0 disables it
@@ -586,6 +587,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       S.swapflag_peers[r] = base ? (uint32_t*)(base + e->off_swapflag[par]) : nullptr;
       S.sc_rowbuf_peers[r] = base ? (double*)(base + e->off_rowbuf[spar]) : nullptr;
       S.sc_rowflag_peers[r] = base ? (uint32_t*)(base + e->off_rowflag[spar]) : nullptr;
+      S.stepdone_peers[r] = base ? (uint32_t*)(base + e->off_stepdone) : nullptr;
     }
     S.rowbuf_mc = e->symm_mc ? (double*)(e->symm_mc + e->off_rowbuf[par]) : nullptr;
     S.rowflag_mc = e->symm_mc ? (uint32_t*)(e->symm_mc + e->off_rowflag[par]) : nullptr;

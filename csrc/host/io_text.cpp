@@ -80,6 +80,36 @@ int jb_read_matrix_rows(const char* path, int64_t n, int64_t row0, int64_t nrows
   return 0;
 }
 
+// Streaming reader: the file is scanned once, a caller-chosen number of values at a time (the
+// reference reads one block row of m*n numbers, sends it on, and re-uses the buffer,
+// main.cpp:249-263) - the reading rank never holds more than one block row.
+struct JbMatrixReader {
+  FILE* f;
+  Scanner sc;
+  explicit JbMatrixReader(FILE* fp) : f(fp), sc(fp) { sc.buf[0] = 0; }
+};
+
+int jb_matrix_reader_open(const char* path, JbMatrixReader** out) {
+  *out = nullptr;
+  FILE* f = fopen(path, "r");
+  if (!f) return -1;
+  *out = new JbMatrixReader(f);
+  return 0;
+}
+
+int jb_matrix_reader_next(JbMatrixReader* r, int64_t count, double* out) {
+  if (!r) return -1;
+  for (int64_t i = 0; i < count; ++i)
+    if (r->sc.next(out + i) != 1) return -2;
+  return 0;
+}
+
+void jb_matrix_reader_close(JbMatrixReader* r) {
+  if (!r) return;
+  fclose(r->f);
+  delete r;
+}
+
 int jb_read_matrix_full(const char* path, int64_t n, double* out) {
   return jb_read_matrix_rows(path, n, 0, n, out);
 }

@@ -59,6 +59,12 @@ struct StepParams {
   uint32_t tag;           // swapflag value for this step
   int phase;              // JB_PHASE_*
   int pct0, pct1;         // priority column tiles (cover block column t+1); empty if pct1 < pct0
+  // Cross-rank "step finished" tags (symmetric region): stepdone_peers[r][q] on rank r holds the tag
+  // of the last step whose bulk update rank q has completely retired (B1 and B2).  With phase A and
+  // K1 running ahead of the bulk, the min-loc exchange no longer implies that every rank is done
+  // with step t-2, so whoever overwrites a parity-double-buffered peer buffer of step t (SCALE into
+  // rowbuf/rowflag, ROWT push into the pivot owner's swapbuf) first waits for tag(t-2) there.
+  uint32_t* stepdone_peers[JB_MAX_RANKS];
   int prev_pct0, prev_pct1;  // phase A: priority range of the previous step; tiles outside it are
   uint32_t prev_tag;         // B1(t-1)'s early tiles, complete once early[8 + j] >= prev_tag
   int nb1;                // look-ahead: the first nb1 non-priority column tiles belong to phase B1

@@ -45,6 +45,7 @@ __device__ __forceinline__ void st_f64x2(double* p, double x, double y) {
 //      Thread -> (column pair v, row parity); 4 independent 16-byte loads in flight per thread.
 //      Not inlined: its address arithmetic must not compete for registers with the DMMA loop.
 __device__ __noinline__ void rowt_item(double* wrow, double* swap_dst, uint32_t* swap_flag,
+                                       const uint32_t* dest_done, uint32_t dest_want,
                                        const double* src, const uint32_t* row_flag, uint32_t row_expect,
                                        uint32_t tag, int rows_valid, int ncol, int64_t ldw,
                                        int* abort_flag, unsigned long long spin_to) {
@@ -55,7 +56,12 @@ __device__ __noinline__ void rowt_item(double* wrow, double* swap_dst, uint32_t*
   wrow += 2 * v;
   src += 2 * v;
   if (swap_dst) {
-    // the old block row t goes to the pivot owner's swap buffer over NVLink (main.cpp:1100-1131)
+    // the old block row t goes to the pivot owner's swap buffer over NVLink (main.cpp:1100-1131);
+    // the buffer (parity t & 1) was last used by step t-2: the owner must have retired that step
+    if (dest_done) {
+      if (lane == 0) wait_flag_ge(dest_done, dest_want, abort_flag, spin_to);
+      __syncwarp();
+    }
     double* dst = swap_dst + 2 * v;
     for (int r0 = rh; r0 < rows_valid; r0 += 8) {
       double2 x[4];
@@ -96,6 +102,17 @@ __device__ __forceinline__ void b1_retire(const StepParams& P) {
     st_release_sys_u32(P.b1sync + 1, P.tag);
   }
 }
+// ... and of phase B2: the last one waits for B1(t) (an earlier launch that never waits for B2) and
+// tells every rank that this rank has retired the bulk of step t.
+__device__ __forceinline__ void b2_retire(const StepParams& P) {
+  const uint32_t old = atomicAdd(P.b1sync + 2, 1u);
+  if (old == gridDim.x - 1) {
+    P.b1sync[2] = 0;
+    wait_flag_ge(P.b1sync + 1, P.tag, const_cast<int*>(&P.ctl->timeout_flag), P.ctl->spin_timeout_ns);
+    __threadfence_system();
+    for (int q = 0; q < P.p; ++q) st_release_sys_u32(P.stepdone_peers[q] + P.rank, P.tag);
+  }
+}
 
 // kMode selects which item kinds a launch can contain (bit 0: SCALE, bit 1: ROWT; UPD always), so
 // that code a phase never runs is compiled out and cannot disturb the register allocation of the
@@ -128,6 +145,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
   const Plan pl = make_plan(P, si, sn);
   if (pl.total == 0) {
     if (kRowt && !kScale && P.phase == JB_PHASE_B1 && P.b1sync && tid == 0) b1_retire(P);
+    if (kScale && !kRowt && P.phase == JB_PHASE_B2 && P.b1sync && tid == 0) b2_retire(P);
     return;
   }
   const int sc_slot = (P.sc_t == P.t) ? si.piv_slot : sn.piv_slot;  // pivot row the SCALE items read
@@ -171,6 +189,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
       tma_prefetch_desc(&M.tmInv);
       tma_prefetch_desc(&M.tmSwap);
       uint32_t it_cnt = 0;
+      bool peers_done = false;
       for (uint32_t rp = 0;; ++rp) {
         const int idx = (int)atomicAdd(P.counter, 1u);
         const int slot = rp % RING;
@@ -201,6 +220,13 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           // K1(t+1)).  The rest belongs to phase B1, which may still be running beside us but never
           // waits for this launch: its first `nearly` tiles are flagged one by one, for the others
           // wait until its last CTA has retired.
+          if (!peers_done && P.t > 0) {
+            // rowbuf / rowflag of step t+1 (parity (t+1) & 1) were last read by step t-1: every rank
+            // must have retired it before the first tile is overwritten
+            for (int q = 0; q < P.p; ++q)
+              wait_flag_ge(P.stepdone_peers[P.rank] + q, P.tag - 1, abort_flag, spin_to);
+            peers_done = true;
+          }
           const bool pri = pl.npri > 0 && it.ct >= P.pct0 && it.ct <= P.pct1;
           if (!pri) {
             const int pos = np_pos(P, pl, it.ct);
@@ -266,6 +292,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
       rowt_item(P.W + (int64_t)P.t_slot * P.m * P.ldw + roff,
                 si.do_swap ? P.swapbuf_peers[si.piv_rank] + roff : nullptr,
                 si.do_swap ? P.swapflag_peers[si.piv_rank] + it.ct * P.nsub + it.sub : nullptr,
+                (P.b1sync && P.t >= 2) ? P.stepdone_peers[P.rank] + si.piv_rank : nullptr, P.tag - 2,
                 rowbuf_local + roff, rowflag_local + it.ct, P.row_expect, P.tag, it.rows_valid, ncol,
                 P.ldw, abort_flag, spin_to);
       continue;
@@ -412,6 +439,11 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
     __threadfence();
     named_bar_sync(1, MMA_WARPS * 32);
     if (tid == 0) b1_retire(P);
+  }
+  if (kScale && !kRowt && P.phase == JB_PHASE_B2 && P.b1sync) {
+    __threadfence();
+    named_bar_sync(1, MMA_WARPS * 32);
+    if (tid == 0) b2_retire(P);
   }
 }
 

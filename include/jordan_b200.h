@@ -44,6 +44,12 @@ double jb_formula(int id, int64_t i, int64_t j, int64_t n);
  * Returns 0, -1 cannot open, -2 cannot read (short / garbled file). */
 int jb_read_matrix_rows(const char* path, int64_t n, int64_t row0, int64_t nrows, double* out);
 int jb_read_matrix_full(const char* path, int64_t n, double* out);
+/* Streaming form (one scan of the file, `count` values per call, e.g. one block row = h*n): what
+ * read_matrix does with its m*n buffer, main.cpp:249-263.  open: 0 / -1; next: 0 / -2. */
+typedef struct JbMatrixReader JbMatrixReader;
+int jb_matrix_reader_open(const char* path, JbMatrixReader** out);
+int jb_matrix_reader_next(JbMatrixReader* r, int64_t count, double* out);
+void jb_matrix_reader_close(JbMatrixReader* r);
 /* print_row main.cpp:284-295: "%.2f\t" per value, "\n" per row, into a caller buffer. */
 int64_t jb_format_corner(const double* a, int64_t rows, int64_t cols, int64_t ld, char* buf,
                          int64_t buflen);
@@ -96,6 +102,31 @@ int jb_engine_bind_symm(JbEngine* e, void* const* peer_ptrs, void* multicast_ptr
  * handle: 64 bytes (cudaIpcMemHandle_t). */
 int jb_engine_ipc_handle(JbEngine* e, int which, void* handle64);
 int jb_engine_open_peers(JbEngine* e, int which, const void* handles /* p * 64 bytes */);
+/* Native symmetric heap (csrc/comm/symm_heap.cpp; no counterpart in the reference, which keeps
+ * everything in host memory and exchanges it with MPI_Bcast / MPI_Send, main.cpp:1097, 1122-1129):
+ * one cuMemCreate allocation per rank, shared as POSIX file descriptors that the CALLER moves between
+ * the rank processes (SCM_RIGHTS over Unix sockets: jb_mpi_send_fd / jb_mpi_recv_fd of the MPI shim,
+ * or parallel/comm.py under torchrun), mapped on every rank, plus an NVLS multicast alias
+ * (cuMulticastCreate / AddDevice / BindMem) where the GPUs sit behind an NVSwitch.  Order of calls:
+ *   create (all)  ->  exchange fds  ->  import (all)
+ *   [multicast]   mc_create (rank 0) -> send fd to all -> mc_import (others) -> mc_add (all)
+ *                 -> barrier -> mc_bind (all) -> barrier;  on any failure: mc_drop on ALL ranks
+ * then hand the pointers to jb_engine_bind_symm.  The heap must outlive the engine. */
+typedef struct JbSymmHeap JbSymmHeap;
+int jb_symm_heap_create(size_t bytes, int device, int rank, int size, int want_multicast,
+                        JbSymmHeap** out, int* export_fd);
+int jb_symm_heap_import(JbSymmHeap* h, const int* fds /* [size], closed by the call */);
+int jb_symm_heap_multicast_supported(const JbSymmHeap* h);
+int jb_symm_heap_mc_create(JbSymmHeap* h, int* export_fd);
+int jb_symm_heap_mc_import(JbSymmHeap* h, int fd);
+int jb_symm_heap_mc_add(JbSymmHeap* h);
+int jb_symm_heap_mc_bind(JbSymmHeap* h);
+void jb_symm_heap_mc_drop(JbSymmHeap* h);
+void* jb_symm_heap_ptr(const JbSymmHeap* h, int rank);   /* rank's memory as mapped here */
+void* jb_symm_heap_mc_ptr(const JbSymmHeap* h);          /* multicast alias or NULL */
+size_t jb_symm_heap_bytes(const JbSymmHeap* h);
+void jb_symm_heap_destroy(JbSymmHeap* h);
+
 /* Zero flags / mailboxes / step counter.  Call on all ranks, then barrier, e.g. after a singular
  * verdict left the step epochs of the ranks inconsistent. */
 int jb_engine_reset_sync(JbEngine* e);

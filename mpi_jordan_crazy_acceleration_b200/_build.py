@@ -33,6 +33,8 @@ CUDA_SRCS = [
     "csrc/dist_gemm.cu",
     "csrc/engine.cu",
 ]
+# host-only translation units that need the CUDA headers: part of libjordan_b200.so only
+CUDA_HOST_SRCS = ["csrc/comm/symm_heap.cpp"]
 CUDA_HDRS = ["csrc/common.cuh", "csrc/kernels.h", "csrc/kernels_formula.h", "csrc/engine_types.h", "csrc/step_plan.h",
              "include/jordan_b200.h"]
 
@@ -79,7 +81,7 @@ def build_cuda(force: bool = False) -> Path:
             _run([NVCC, *NVCC_FLAGS, "-c", src, "-o", str(obj)], log=OBJDIR / (Path(src).stem + ".ptxas.log"))
         objs.append(str(obj))
     host_objs = []
-    for src in HOST_SRCS:
+    for src in HOST_SRCS + CUDA_HOST_SRCS:
         obj = OBJDIR / (Path(src).stem + ".host.o")
         if force or _newer(obj, [ROOT / src, *hdrs]):
             _run([CXX, *CXX_FLAGS, "-c", src, "-o", str(obj)])

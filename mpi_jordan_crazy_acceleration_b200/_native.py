@@ -61,6 +61,9 @@ def _declare_host(lib) -> None:
         "jb_formula": (dbl, [C.c_int, i64, i64, i64]),
         "jb_read_matrix_rows": (C.c_int, [C.c_char_p, i64, i64, i64, C.c_void_p]),
         "jb_read_matrix_full": (C.c_int, [C.c_char_p, i64, C.c_void_p]),
+        "jb_matrix_reader_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+        "jb_matrix_reader_next": (C.c_int, [C.c_void_p, i64, C.c_void_p]),
+        "jb_matrix_reader_close": (None, [C.c_void_p]),
         "jb_format_corner": (i64, [C.c_void_p, i64, i64, i64, C.c_char_p, i64]),
         "jb_cpu_block_jordan": (C.c_int, [C.c_void_p, C.c_void_p, i64, i64, i64, C.c_void_p]),
         "jb_cpu_inverse_block": (C.c_int, [C.c_void_p, C.c_void_p, dbl, i64]),
@@ -99,6 +102,19 @@ def _declare_cuda(lib) -> None:
         "jb_engine_pivots": (C.c_int, [vp, vp]),
         "jb_engine_launch_count": (i64, [vp]),
         "jb_engine_set_profiling": (C.c_int, [vp, C.c_int]),
+        "jb_symm_heap_create": (C.c_int, [C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp),
+                                          C.POINTER(C.c_int)]),
+        "jb_symm_heap_import": (C.c_int, [vp, C.POINTER(C.c_int)]),
+        "jb_symm_heap_multicast_supported": (C.c_int, [vp]),
+        "jb_symm_heap_mc_create": (C.c_int, [vp, C.POINTER(C.c_int)]),
+        "jb_symm_heap_mc_import": (C.c_int, [vp, C.c_int]),
+        "jb_symm_heap_mc_add": (C.c_int, [vp]),
+        "jb_symm_heap_mc_bind": (C.c_int, [vp]),
+        "jb_symm_heap_mc_drop": (None, [vp]),
+        "jb_symm_heap_ptr": (vp, [vp, C.c_int]),
+        "jb_symm_heap_mc_ptr": (vp, [vp]),
+        "jb_symm_heap_bytes": (C.c_size_t, [vp]),
+        "jb_symm_heap_destroy": (None, [vp]),
         "jb_engine_phase_times": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "jb_engine_w_ptr": (vp, [vp]),
         "jb_engine_ldw": (i64, [vp]),

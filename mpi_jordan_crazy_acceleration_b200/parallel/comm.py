@@ -82,6 +82,70 @@ class Comm:
         dist.broadcast_object_list(box, src=src, group=self.ctrl)
         return box[0]
 
+    # ------------------------------------------------------------ file descriptors (same host)
+    def _fd_sock_name(self, rank: int, tag: str) -> str:
+        port = os.environ.get("MASTER_PORT", "0")
+        return f"\0jb_fd_{os.getuid()}_{port}_{tag}_{rank}"   # abstract namespace: nothing to unlink
+
+    def exchange_fds(self, fd: int, tag: str = "x") -> list[int]:
+        """All-to-all of one open file descriptor per rank (SCM_RIGHTS over abstract Unix sockets):
+        the channel that carries CUDA VMM allocation handles between the rank processes of one
+        host (csrc/comm/symm_heap.cpp).  Returns the received descriptors, own slot = ``fd``."""
+        import socket
+
+        if not self.enabled or self.world == 1:
+            return [fd]
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(self._fd_sock_name(self.rank, tag))
+        srv.listen(self.world)
+        self.barrier()                      # every rank listens before anybody connects
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(self._fd_sock_name(r, tag))
+            socket.send_fds(c, [self.rank.to_bytes(4, "little")], [fd])
+            c.close()
+        out = [-1] * self.world
+        out[self.rank] = fd
+        for _ in range(self.world - 1):
+            conn, _addr = srv.accept()
+            msg, fds, _flags, _a = socket.recv_fds(conn, 4, 1)
+            out[int.from_bytes(msg, "little")] = fds[0]
+            conn.close()
+        srv.close()
+        self.barrier()
+        return out
+
+    def bcast_fd(self, fd: int, src: int = 0, tag: str = "b") -> int:
+        """One descriptor from ``src`` to every rank (the multicast object's handle)."""
+        import socket
+
+        if not self.enabled or self.world == 1:
+            return fd
+        if self.rank != src:
+            srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            srv.bind(self._fd_sock_name(self.rank, tag))
+            srv.listen(1)
+        self.barrier()
+        got = fd
+        if self.rank == src:
+            for r in range(self.world):
+                if r == src:
+                    continue
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.connect(self._fd_sock_name(r, tag))
+                socket.send_fds(c, [b"m"], [fd])
+                c.close()
+        else:
+            conn, _addr = srv.accept()
+            _msg, fds, _flags, _a = socket.recv_fds(conn, 1, 1)
+            got = fds[0]
+            conn.close()
+            srv.close()
+        self.barrier()
+        return got
+
     def send_tensor(self, t: torch.Tensor, dst: int) -> None:
         dist.send(t, dst=dst, group=self.ctrl)
 

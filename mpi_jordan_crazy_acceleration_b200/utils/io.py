@@ -44,40 +44,47 @@ def write_matrix(path: str, a: torch.Tensor) -> None:
 
 def scatter_text_matrix(path: str, layout: Layout, comm: Comm, reader: int = 0,
                         pin: bool = False) -> torch.Tensor:
-    """Returns this rank's ``rows_real x n`` rows.  All ranks agree on errors (C3)."""
+    """Returns this rank's ``rows_real x n`` rows.  The reading rank scans the file ONCE and holds a
+    single block row (``m*n`` numbers) at a time, which it keeps or sends to the owner - the
+    reference's streaming scatter (``main.cpp:249-263``), not a full ``n*n`` staging copy.  All ranks
+    agree on errors (C3); a short or garbled file stops the scatter at the block row where it is
+    detected (fail fast)."""
     n, m, p = layout.n, layout.m, layout.p
+    lib = _native.host()
     local = torch.empty(layout.rows_real, n, dtype=torch.float64)
     if pin and torch.cuda.is_available():
         local = local.pin_memory()
+    rd = C.c_void_p()
     err = 0
-    if comm.world == 1:
-        if layout.rows_real:
-            err = _native.host().jb_read_matrix_rows(path.encode(), n, 0, n, C.c_void_p(local.data_ptr()))
-        if err:
-            raise MatrixFileError(err, path)
-        return local
-    full = None
     if comm.rank == reader:
-        # fail fast (SURVEY D12): validate the whole file before anything is sent
-        full = torch.empty(n, n, dtype=torch.float64)
-        err = _native.host().jb_read_matrix_full(path.encode(), n, C.c_void_p(full.data_ptr()))
+        err = lib.jb_matrix_reader_open(path.encode(), C.byref(rd))
     err = comm.bcast_obj(err, src=reader)
     if err:
         raise MatrixFileError(err, path)
-    for I in range(layout.Nr):
-        owner = I % p
-        h = min(m, n - I * m)
-        slot = I // p
-        if comm.rank == reader:
-            blk = full[I * m: I * m + h].contiguous()
-            if owner == reader:
-                local[slot * m: slot * m + h] = blk
-            else:
-                comm.send_tensor(blk, owner)
-        elif comm.rank == owner:
-            buf = torch.empty(h, n, dtype=torch.float64)
-            comm.recv_tensor(buf, reader)
-            local[slot * m: slot * m + h] = buf
+    blk = torch.empty(m, n, dtype=torch.float64)
+    try:
+        for I in range(layout.Nr):
+            owner = I % p
+            h = min(m, n - I * m)
+            slot = I // p
+            if comm.rank == reader:
+                err = lib.jb_matrix_reader_next(rd, h * n, C.c_void_p(blk.data_ptr()))
+            if comm.world > 1:
+                err = comm.bcast_obj(err, src=reader)
+            if err:
+                raise MatrixFileError(err, path)
+            if comm.rank == reader:
+                if owner == reader:
+                    local[slot * m: slot * m + h] = blk[:h]
+                else:
+                    comm.send_tensor(blk[:h].contiguous(), owner)
+            elif comm.rank == owner:
+                buf = torch.empty(h, n, dtype=torch.float64)
+                comm.recv_tensor(buf, reader)
+                local[slot * m: slot * m + h] = buf
+    finally:
+        if comm.rank == reader and rd:
+            lib.jb_matrix_reader_close(rd)
     return local
 
 

@@ -65,6 +65,13 @@ int MPI_Type_free(MPI_Datatype* type);
 int MPI_Op_create(MPI_User_function* fn, int commute, MPI_Op* op);
 int MPI_Op_free(MPI_Op* op);
 
+/* Extension of the shim (no MPI counterpart): hand an open file descriptor to another rank on the
+ * same host (SCM_RIGHTS over the pair's socket).  Returns 0 / the received descriptor, -1 on error.
+ * A build against a real MPI has no such channel: test JB_MPI_SHIM_HAS_FD_PASSING. */
+#define JB_MPI_SHIM_HAS_FD_PASSING 1
+int jb_mpi_send_fd(int fd, int dest);
+int jb_mpi_recv_fd(int src);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,6 +31,7 @@ struct Peer {
   int fd = -1;
   std::string inbox;  // raw bytes received but not yet consumed
   size_t inpos = 0;
+  std::deque<int> fds;  // descriptors that arrived as SCM_RIGHTS ancillary data (jb_mpi_recv_fd)
 };
 
 int g_rank = 0, g_size = 1;
@@ -68,12 +69,38 @@ void compact(Peer& p) {
   }
 }
 
+// recv() that also collects file descriptors passed along with the bytes (SCM_RIGHTS).  Every read
+// of a peer socket goes through here: a plain recv() would silently drop (and close) descriptors
+// attached to the bytes it returns.
+ssize_t recv_with_fds(Peer& p, void* buf, size_t len, int flags) {
+  iovec iov;
+  iov.iov_base = buf;
+  iov.iov_len = len;
+  alignas(cmsghdr) char ctrl[CMSG_SPACE(8 * sizeof(int))];
+  msghdr mh;
+  memset(&mh, 0, sizeof(mh));
+  mh.msg_iov = &iov;
+  mh.msg_iovlen = 1;
+  mh.msg_control = ctrl;
+  mh.msg_controllen = sizeof(ctrl);
+  ssize_t r = recvmsg(p.fd, &mh, flags | MSG_CMSG_CLOEXEC);
+  if (r > 0)
+    for (cmsghdr* c = CMSG_FIRSTHDR(&mh); c; c = CMSG_NXTHDR(&mh, c))
+      if (c->cmsg_level == SOL_SOCKET && c->cmsg_type == SCM_RIGHTS) {
+        const size_t nfd = (c->cmsg_len - CMSG_LEN(0)) / sizeof(int);
+        int got[8];
+        memcpy(got, CMSG_DATA(c), nfd * sizeof(int));
+        for (size_t i = 0; i < nfd; ++i) p.fds.push_back(got[i]);
+      }
+  return r;
+}
+
 // read whatever is available on fd into the peer's inbox (non-blocking)
 bool drain(Peer& p) {
   char buf[1 << 16];
   bool any = false;
   for (;;) {
-    ssize_t r = recv(p.fd, buf, sizeof(buf), MSG_DONTWAIT);
+    ssize_t r = recv_with_fds(p, buf, sizeof(buf), MSG_DONTWAIT);
     if (r > 0) {
       p.inbox.append(buf, (size_t)r);
       any = true;
@@ -137,7 +164,7 @@ void recv_exact(int src, void* out, size_t len) {
       continue;
     }
     // large payloads: read straight into the user buffer
-    ssize_t r = recv(s.fd, o, len, 0);
+    ssize_t r = recv_with_fds(s, o, len, 0);
     if (r > 0) {
       o += r;
       len -= (size_t)r;
@@ -331,6 +358,58 @@ int MPI_Allgather(const void* sendbuf, int sendcount, MPI_Datatype sendtype, voi
                   int recvcount, MPI_Datatype recvtype, MPI_Comm) {
   MPI_Gather(sendbuf, sendcount, sendtype, recvbuf, recvcount, recvtype, 0, MPI_COMM_WORLD);
   return MPI_Bcast(recvbuf, recvcount * g_size, recvtype, 0, MPI_COMM_WORLD);
+}
+
+// ---- extension (not MPI): pass an open file descriptor to another rank of the same host.  Used to
+// share CUDA VMM allocations between the rank processes (csrc/comm/symm_heap.cpp).  The descriptor
+// rides as SCM_RIGHTS ancillary data on the one payload byte of an ordinary framed message, so it
+// stays in order with every other message of the pair.
+int jb_mpi_send_fd(int fd, int dest) {
+  if (dest == g_rank || dest < 0 || dest >= g_size) return -1;
+  Header h;
+  h.tag = -12;
+  h.pad = 0;
+  h.bytes = 1;
+  send_all(dest, &h, sizeof(h));
+  char byte = 'F';
+  iovec iov;
+  iov.iov_base = &byte;
+  iov.iov_len = 1;
+  alignas(cmsghdr) char ctrl[CMSG_SPACE(sizeof(int))];
+  memset(ctrl, 0, sizeof(ctrl));
+  msghdr mh;
+  memset(&mh, 0, sizeof(mh));
+  mh.msg_iov = &iov;
+  mh.msg_iovlen = 1;
+  mh.msg_control = ctrl;
+  mh.msg_controllen = sizeof(ctrl);
+  cmsghdr* c = CMSG_FIRSTHDR(&mh);
+  c->cmsg_level = SOL_SOCKET;
+  c->cmsg_type = SCM_RIGHTS;
+  c->cmsg_len = CMSG_LEN(sizeof(int));
+  memcpy(CMSG_DATA(c), &fd, sizeof(int));
+  for (;;) {
+    ssize_t w = sendmsg(g_peers[dest].fd, &mh, MSG_NOSIGNAL);  // blocking: one byte
+    if (w == 1) return 0;
+    if (w < 0 && (errno == EINTR)) continue;
+    if (w < 0 && (errno == EAGAIN || errno == EWOULDBLOCK)) {
+      for (int r = 0; r < g_size; ++r)
+        if (r != g_rank) drain(g_peers[r]);
+      continue;
+    }
+    die("sendmsg(SCM_RIGHTS)");
+  }
+}
+
+int jb_mpi_recv_fd(int src) {
+  if (src == g_rank || src < 0 || src >= g_size) return -1;
+  char byte = 0;
+  p2p_recv(&byte, 1, src, -12, nullptr);
+  Peer& p = g_peers[src];
+  if (p.fds.empty()) return -1;
+  int fd = p.fds.front();
+  p.fds.pop_front();
+  return fd;
 }
 
 int MPI_Address(void* location, MPI_Aint* address) { *address = (MPI_Aint)location; return MPI_SUCCESS; }

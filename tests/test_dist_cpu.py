@@ -46,7 +46,17 @@ try:
 except jio.MatrixFileError as exc:
     err = exc.code
 codes = comm.allgather_obj(err)
+# descriptor passing between the rank processes (carries CUDA VMM handles on the GPU box)
+import tempfile
+tf = tempfile.TemporaryFile()
+tf.write(b"rank%%d" %% comm.rank); tf.flush()
+fds = comm.exchange_fds(tf.fileno(), tag="t1")
+seen = [os.pread(fd, 16, 0).decode() for fd in fds]
+bfd = comm.bcast_fd(tf.fileno(), src=comm.world - 1, tag="t2")
+seen.append(os.pread(bfd, 16, 0).decode())
+fd_ok = comm.allgather_obj(seen == ["rank%%d" %% r for r in range(comm.world)] + ["rank%%d" %% (comm.world - 1)])
 if comm.rank == 0:
+    out.append({"fd_ok": fd_ok})
     out.append({"file": True, "X": X.tolist(), "corner": c.tolist(), "piv": e.pivots, "codes": codes})
     print("RESULT " + json.dumps(out))
 '''
@@ -69,7 +79,8 @@ def test_eager_gloo_world(world, tmp_path):
     import json
 
     res = json.loads(line[-1][7:])
-    for rec in res[:-1]:
+    assert res[-2] == {"fd_ok": [True] * world}
+    for rec in res[:-2]:
         A_f = formula_rows(rec["fid"], rec["n"], torch.arange(rec["n"]))
         Xo, piv = cpu_block_jordan(A_f, rec["m"], world)      # oracle emulating `world` ranks
         assert rec["piv"] == piv

@@ -22,7 +22,7 @@ def _run(nproc, mode, extra_env=None):
     return json.loads(line[-1][len("MPRESULT "):])
 
 
-@pytest.mark.parametrize("mode", ["auto", "ipc"])
+@pytest.mark.parametrize("mode", ["auto", "ipc", "torch"])
 def test_multi_gpu_matches_oracle(mode):
     ng = torch.cuda.device_count()
     if ng < 2:

@@ -85,3 +85,60 @@ def test_launcher_propagates_exit_codes(tmp_path):
     subprocess.run(["g++", "-I", os.path.join(ROOT, "mpi_shim"), str(src), lib, "-o", str(exe)], check=True)
     r = subprocess.run([os.path.join(ROOT, "bin", "jb_mpirun"), "-np", "3", str(exe)])
     assert r.returncode == 2
+
+
+FD_PROG = r'''
+#include "mpi.h"
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+#include <vector>
+// every rank writes its number into an unlinked temp file and hands the DESCRIPTOR to every other
+// rank (the channel csrc/comm/symm_heap.cpp uses for CUDA VMM handles); interleaved with ordinary
+// messages to check that descriptors stay in order with the byte stream
+int main(int argc, char** argv) {
+  MPI_Init(&argc, &argv);
+  int p, k; MPI_Comm_size(MPI_COMM_WORLD, &p); MPI_Comm_rank(MPI_COMM_WORLD, &k);
+  char name[] = "/tmp/jbfdXXXXXX";
+  int fd = mkstemp(name); unlink(name);
+  int payload = 1000 + k;
+  if (write(fd, &payload, sizeof(payload)) != (ssize_t)sizeof(payload)) return 9;
+  int bad = 0;
+  std::vector<double> big(1 << 18, (double)k);
+  for (int r = 0; r < p; ++r) if (r != k) {
+    MPI_Send(&k, 1, MPI_INT, r, 5, MPI_COMM_WORLD);
+    if (jb_mpi_send_fd(fd, r) != 0) bad |= 1;
+    MPI_Send(big.data(), (int)big.size(), MPI_DOUBLE, r, 6, MPI_COMM_WORLD);
+  }
+  for (int r = 0; r < p; ++r) if (r != k) {
+    int who = -1; MPI_Recv(&who, 1, MPI_INT, r, 5, MPI_COMM_WORLD, MPI_STATUS_IGNORE);
+    int got = jb_mpi_recv_fd(r);
+    std::vector<double> in(big.size());
+    MPI_Recv(in.data(), (int)in.size(), MPI_DOUBLE, r, 6, MPI_COMM_WORLD, MPI_STATUS_IGNORE);
+    int val = -1;
+    if (who != r || got < 0 || pread(got, &val, sizeof(val), 0) != (ssize_t)sizeof(val) || val != 1000 + r) bad |= 2;
+    if (in[0] != (double)r || in.back() != (double)r) bad |= 4;
+    if (got >= 0) close(got);
+  }
+  int tot = 0; MPI_Allreduce(&bad, &tot, 1, MPI_INT, MPI_SUM, MPI_COMM_WORLD);
+  if (k == 0) printf("fd-check p=%d bad=%d\n", p, tot);
+  MPI_Finalize();
+  return tot ? 3 : 0;
+}
+'''
+
+
+@pytest.mark.parametrize("p", [2, 4])
+def test_shim_passes_file_descriptors(p, tmp_path):
+    from mpi_jordan_crazy_acceleration_b200 import _build
+
+    _build.build_shim()
+    src = tmp_path / "fd.cpp"
+    src.write_text(FD_PROG)
+    exe = tmp_path / "fd.out"
+    lib = os.path.join(ROOT, "mpi_jordan_crazy_acceleration_b200", "lib", "libjbmpi.a")
+    subprocess.run(["g++", "-O1", "-I", os.path.join(ROOT, "mpi_shim"), str(src), lib, "-o", str(exe)], check=True)
+    r = subprocess.run([os.path.join(ROOT, "bin", "jb_mpirun"), "-np", str(p), str(exe)], capture_output=True,
+                       text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert f"fd-check p={p} bad=0" in r.stdout
