@@ -282,16 +282,22 @@ def pivoting_check(args, comm, local_rank) -> dict:
 
 
 def run_baseline(args) -> dict:
+    """In-tree NCCL + cuBLAS implementation of the same algorithm (baseline/nccl_cublas/jordan_nccl.py):
+    batched LU inversion of the candidates, NCCL all_gather / broadcast / send-recv, one DGEMM
+    (addmm_) per step.  The baseline the engine is compared against - never the product path."""
     import torch
+    import torch.distributed as dist
 
-    from mpi_jordan_crazy_acceleration_b200.models.eager import EagerJordan
+    sys.path.insert(0, os.path.join(ROOT, "baseline", "nccl_cublas"))
+    from jordan_nccl import NcclCublasJordan
+
     from mpi_jordan_crazy_acceleration_b200.parallel.comm import Comm
 
     comm = Comm.init_from_env()
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
     n, m, W, K = args.n, args.m, args.warmup, args.steps
-    e = EagerJordan(n, m, comm=comm, device=f"cuda:{local_rank}")
+    e = NcclCublasJordan(n, m, device=f"cuda:{local_rank}")
 
     def one_step():
         e.fill_formula(args.formula)
@@ -312,7 +318,11 @@ def run_baseline(args) -> dict:
     out = {"metric": METRIC, "value": flops(n) / (ms * 1e-3) / 1e9, "unit": "GFLOP/s",
            "n_gpus": comm.world, "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True,
            "scaling": "strong", "vs_baseline": None, "dtype": "fp64", "data": "synthetic",
-           "impl": "baseline-nccl-cublas", "config": {"n": n, "m": m}}
+           "impl": "baseline-nccl-cublas",
+           "config": {"n": n, "m": m, "model": "block Gauss-Jordan inverse, generator |i-j|, in-place 2n^3 form",
+                      "libraries": "torch.linalg.inv_ex (batched LU), torch.addmm_ (cuBLAS DGEMM), "
+                                   "NCCL all_gather / broadcast / send / recv",
+                      "nccl": ".".join(map(str, torch.cuda.nccl.version())) if dist.is_initialized() else None}}
     return out if comm.rank == 0 else {}
 
 
