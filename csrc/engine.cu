@@ -642,7 +642,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       const int kk = std::min(128, e->m - kb * 128);
       JB_CHECK(jb_tc05_slice_cols(rowbuf + (int64_t)kb * 128 * e->ldw, e->ldw, e->ldw, kk, e->tc_slices,
                                   e->Rq[kb], e->cols_pad, e->cscale[kb], rowflag,
-                                  ((g >> 1) + 1) * (uint32_t)e->nsub, s));
+                                  ((g >> 1) + 1) * (uint32_t)e->nsub, e->ctl, s));
       Tc05Launch a;
       memset(&a, 0, sizeof(a));
       a.C = e->W; a.ldc = e->ldw; a.rows = e->rows_loc; a.cols = e->ldw; a.Lq = e->Lq[par][kb];
@@ -1004,8 +1004,12 @@ int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double 
   const size_t inv_bytes = (size_t)nblocks * Kp * Kp * 8;
   const size_t lbuf_bytes = (size_t)nblocks * m * Kp * 8;
   const size_t total = inv_bytes + lbuf_bytes + 4096 + (size_t)sizeof(JbStepInfo) * 2;
-  JB_CHECK(cudaMalloc((void**)&scratch, total));
-  JB_CHECK(cudaMemsetAsync(scratch, 0, total, st));
+  if (cudaMalloc((void**)&scratch, total) != cudaSuccess) {
+    jb_set_error("Not enough memory! (block inversion staging, %zu bytes)", total);
+    return JB_ERR_NOMEM;
+  }
+  // every exit below goes through `done`, so the staging area is released on errors too
+  cudaError_t ce = cudaSuccess;
   K1Params K;
   memset(&K, 0, sizeof(K));
   K.W = d_blocks;
@@ -1019,15 +1023,19 @@ int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double 
   K.okbuf = d_ok;
   K.ldw = m; K.m = m; K.Kp = Kp; K.p = 1; K.rank = 0; K.t = 0; K.rloc = (int)nblocks;
   K.s0 = 0; K.ncand = (int)nblocks; K.ngroups = (int)nblocks; K.tag = 1;
-  JB_CHECK(cudaMemcpyAsync(&K.ctl->norm_a, &norm_a, 8, cudaMemcpyHostToDevice, st));
-  JB_CHECK(cudaMemsetAsync(d_ok, 0, (size_t)nblocks * 4, st));
-  JB_CHECK(jb_launch_k1(K, 1, st));
-  for (int64_t b = 0; b < nblocks; ++b)
-    JB_CHECK(cudaMemcpy2DAsync(d_inv + b * m * m, (size_t)m * 8, K.invbuf + b * Kp * Kp,
-                               (size_t)Kp * 8, (size_t)m * 8, (size_t)m, cudaMemcpyDeviceToDevice,
-                               st));
-  JB_CHECK(cudaStreamSynchronize(st));
-  JB_CHECK(cudaFree(scratch));
+  do {
+    if ((ce = cudaMemsetAsync(scratch, 0, total, st)) != cudaSuccess) break;
+    if ((ce = cudaMemcpyAsync(&K.ctl->norm_a, &norm_a, 8, cudaMemcpyHostToDevice, st)) != cudaSuccess) break;
+    if ((ce = cudaMemsetAsync(d_ok, 0, (size_t)nblocks * 4, st)) != cudaSuccess) break;
+    if ((ce = jb_launch_k1(K, 1, st)) != cudaSuccess) break;
+    if ((ce = jb_launch_compact_blocks(K.invbuf, Kp, d_inv, m, nblocks, st)) != cudaSuccess) break;
+    ce = cudaStreamSynchronize(st);
+  } while (0);
+  cudaFree(scratch);
+  if (ce != cudaSuccess) {
+    jb_set_error("jb_block_inverse: %s", cudaGetErrorString(ce));
+    return JB_ERR_CUDA;
+  }
   return JB_OK;
 }
 

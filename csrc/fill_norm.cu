@@ -128,3 +128,26 @@ cudaError_t jb_launch_unpermute(double* W, int64_t rows, int64_t ldw, int m, int
   k_unpermute<<<grid, 128, 0, st>>>(W, rows, ldw, m, Nr, stepinfo);
   return cudaGetLastError();
 }
+
+// dst[b][i][j] = src[b][i][j] for i, j < m: blocks stored with pitch Kp (m rounded up to 16) are
+// packed to pitch m in ONE launch (the stand-alone block-inversion entry points return m x m blocks)
+__global__ void k_compact_blocks(const double* __restrict__ src, int Kp, double* __restrict__ dst, int m,
+                                 int64_t nblocks) {
+  const int64_t per = (int64_t)m * m;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nblocks * per;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = e / per;
+    const int r = (int)((e - b * per) / m), c = (int)(e - b * per - (int64_t)r * m);
+    dst[e] = src[(b * Kp + r) * Kp + c];
+  }
+}
+
+cudaError_t jb_launch_compact_blocks(const double* src, int Kp, double* dst, int m, int64_t nblocks,
+                                     cudaStream_t st) {
+  if (nblocks <= 0) return cudaSuccess;
+  const int64_t total = nblocks * m * m;
+  const int grid = (int)(total / 256 + 1 < 148 * 8 ? total / 256 + 1 : 148 * 8);
+  k_compact_blocks<<<grid, 256, 0, st>>>(src, Kp, dst, m, nblocks);
+  return cudaGetLastError();
+}
+

@@ -104,6 +104,10 @@ cudaError_t jb_launch_fill(const FillParams& P, cudaStream_t st);
 cudaError_t jb_launch_rowsum_max(const double* W, int64_t rows, int64_t cols, int64_t ld,
                                  double* out_max, cudaStream_t st);
 
+// blocks with pitch Kp -> packed m x m blocks (stand-alone block inversion entry points)
+cudaError_t jb_launch_compact_blocks(const double* src, int Kp, double* dst, int m, int64_t nblocks,
+                                     cudaStream_t st);
+
 // ------------------------------------------------------------------ final column un-permutation
 cudaError_t jb_launch_unpermute(double* W, int64_t rows, int64_t ldw, int m, int Nr,
                                 const JbStepInfo* stepinfo, cudaStream_t st);
@@ -165,7 +169,7 @@ cudaError_t jb_tc05_slice_rows(const double* L, int64_t ldl, int64_t rows, int K
                                int64_t rows_pad, double* scale, cudaStream_t st);
 cudaError_t jb_tc05_slice_cols(const double* Rn, int64_t ldr, int64_t cols, int K, int S, int8_t* Rq,
                                int64_t cols_pad, double* scale, const uint32_t* flags, uint32_t expect,
-                               cudaStream_t st);
+                               const JbCtl* ctl, cudaStream_t st);
 int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st);
 
 #include "kernels_formula.h"

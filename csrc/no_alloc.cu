@@ -16,8 +16,13 @@
 // threads) race on it - serialise them.
 //
 // Set-up: the first call on a device resolves the device address of the array
-// (cudaGetSymbolAddress with that device current) and remembers it.  Make that first call during
-// initialisation, before any stream capture is started.
+// (cudaGetSymbolAddress with that device current) and remembers it for the life of the process.
+// Make that first call during initialisation, before any stream capture is started.  The
+// remembered address does not survive cudaDeviceReset (the module is reloaded): do not reset a
+// device between calls.
+//
+// Outputs: d_inv holds nblocks packed m x m inverses, d_norms / d_ok nblocks entries each; a block
+// found singular (d_ok = 0) comes back as zeros with norm 0.
 #include <mutex>
 #include <string.h>
 #include "common.cuh"
@@ -106,9 +111,8 @@ extern "C" int jb_block_inverse_noalloc(const double* d_blocks, int64_t nblocks,
   k_noalloc_set_norm<<<1, 1, 0, st>>>(K.ctl, norm_a);
   JB_CHECK(cudaGetLastError());
   JB_CHECK(jb_launch_k1(K, 0, st));
-  for (int64_t b = 0; b < nblocks; ++b)
-    JB_CHECK(cudaMemcpy2DAsync(d_inv + b * m * m, (size_t)m * 8, K.invbuf + b * Kp * Kp,
-                               (size_t)Kp * 8, (size_t)m * 8, (size_t)m, cudaMemcpyDeviceToDevice,
-                               st));
+  // one launch packs all blocks (pitch Kp -> m); a loop of per-block copies would cost up to
+  // thousands of launches for small m, which defeats a latency-critical caller
+  JB_CHECK(jb_launch_compact_blocks(K.invbuf, (int)Kp, d_inv, m, nblocks, st));
   return JB_OK;
 }

@@ -17,6 +17,8 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <mutex>
+#include <vector>
 #include "common.cuh"
 #include "engine_types.h"
 #include "kernels.h"
@@ -75,41 +77,62 @@ __global__ void __launch_bounds__(256) k_slice_rows(const double* __restrict__ L
   }
 }
 
-// one thread per column: Rn[K][cols] (ld = ldr) -> Rq[s][kb][col][128] int8, scale[col] = 2^(e-6)
-__global__ void __launch_bounds__(128) k_slice_cols(const double* __restrict__ Rn, int64_t ldr,
+// Rn[K][cols] (ld = ldr) -> Rq[s][kb][col][128] int8, scale[col] = 2^(e-6).
+// One CTA per 32 columns: the K x 32 panel is read with coalesced 256-byte rows into shared memory,
+// then ONE WARP PER COLUMN slices it - lane l owns k = 4l .. 4l+3 of the 128-deep k-block - so each
+// (slice, column) is written as one 128-byte line.  (A thread-per-column version stored 16 bytes at
+// a 128-byte stride: 8x the sectors, once per step over the whole pivot row.)
+constexpr int SC_COLS = 32;
+__global__ void __launch_bounds__(256) k_slice_cols(const double* __restrict__ Rn, int64_t ldr,
                                                     int64_t cols, int K, int S, int8_t* __restrict__ Rq,
                                                     int64_t cols_pad, double* __restrict__ scale,
-                                                    const uint32_t* flags, uint32_t expect) {
-  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (flags) {  // wait until the pivot-row tile holding my column has landed (owner's SCALE)
-    if (threadIdx.x == 0) wait_flag_ge(flags + (blockIdx.x * blockDim.x) / JB_BN, expect);
+                                                    const uint32_t* flags, uint32_t expect,
+                                                    const JbCtl* ctl) {
+  __shared__ double tile[TC_K][SC_COLS + 1];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t j0 = (int64_t)blockIdx.x * SC_COLS;
+  if (ctl && (ctl->singular | ctl->timeout_flag)) return;
+  if (flags) {  // wait until the pivot-row tile holding my columns has landed (owner's SCALE);
+                // watchdog like every other cross-GPU wait (a dead peer must not hang this GPU)
+    if (tid == 0)
+      wait_flag_ge(flags + j0 / JB_BN, expect, ctl ? const_cast<int*>(&ctl->timeout_flag) : nullptr,
+                   ctl ? ctl->spin_timeout_ns : 0);
     __syncthreads();
+    if (ctl && *(volatile const int*)&ctl->timeout_flag) return;
   }
-  if (j >= cols) return;
   const int KB = (K + TC_K - 1) / TC_K;
-  double amax = 0.0;
-  for (int k = 0; k < K; ++k) amax = fmax(amax, fabs(Rn[(int64_t)k * ldr + j]));
-  const int e = exponent_of(amax);
-  scale[j] = pow2(e - 6);
-  const double up = pow2(6 - e);
   for (int kb = 0; kb < KB; ++kb) {
-    for (int k16 = 0; k16 < TC_K; k16 += 16) {
-      double t[16];
+    __syncthreads();
+    for (int e = tid; e < TC_K * SC_COLS; e += 256) {
+      const int k = e / SC_COLS, c = e % SC_COLS;
+      const int kg = kb * TC_K + k;
+      tile[k][c] = (kg < K && j0 + c < cols) ? Rn[(int64_t)kg * ldr + j0 + c] : 0.0;
+    }
+    __syncthreads();
+    for (int c = warp; c < SC_COLS; c += 8) {
+      const int64_t j = j0 + c;
+      if (j >= cols) break;
+      double t[4];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int k = kb * TC_K + k16 + i;
-        t[i] = (k < K) ? Rn[(int64_t)k * ldr + j] * up : 0.0;
-      }
-      for (int s = 0; s < S; ++s) {
-        uint32_t w[4] = {0, 0, 0, 0};
+      for (int i = 0; i < 4; ++i) t[i] = tile[4 * lane + i][c];
+      // the column's scale comes from ALL k-blocks; KB > 1 callers pass one k-block per launch
+      double amax = fmax(fmax(fabs(t[0]), fabs(t[1])), fmax(fabs(t[2]), fabs(t[3])));
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
+      for (int off = 16; off > 0; off >>= 1) amax = fmax(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+      const int ex = exponent_of(amax);
+      if (lane == 0 && kb == 0) scale[j] = pow2(ex - 6);
+      const double up = pow2(6 - ex);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) t[i] *= up;
+      for (int sl = 0; sl < S; ++sl) {
+        uint32_t w = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
           const double q = rint(t[i]);
-          w[i >> 2] |= ((uint32_t)(uint8_t)(int8_t)(int)q) << (8 * (i & 3));
+          w |= ((uint32_t)(uint8_t)(int8_t)(int)q) << (8 * i);
           t[i] = (t[i] - q) * 128.0;
         }
-        uint4* dst = reinterpret_cast<uint4*>(Rq + (((int64_t)s * KB + kb) * cols_pad + j) * TC_K + k16);
-        *dst = make_uint4(w[0], w[1], w[2], w[3]);
+        reinterpret_cast<uint32_t*>(Rq + (((int64_t)sl * KB + kb) * cols_pad + j) * TC_K)[lane] = w;
       }
     }
   }
@@ -968,22 +991,68 @@ cudaError_t jb_tc05_slice_rows(const double* L, int64_t ldl, int64_t rows, int K
 
 cudaError_t jb_tc05_slice_cols(const double* Rn, int64_t ldr, int64_t cols, int K, int S, int8_t* Rq,
                                int64_t cols_pad, double* scale, const uint32_t* flags, uint32_t expect,
-                               cudaStream_t st) {
+                               const JbCtl* ctl, cudaStream_t st) {
   if (cols == 0) return cudaSuccess;
-  int grid = (int)((cols + 127) / 128);
-  k_slice_cols<<<grid, 128, 0, st>>>(Rn, ldr, cols, K, S, Rq, cols_pad, scale, flags, expect);
+  if (K > TC_K) return cudaErrorInvalidValue;  // one 128-deep k-block per call (the scale is per block)
+  int grid = (int)((cols + SC_COLS - 1) / SC_COLS);
+  k_slice_cols<<<grid, 256, 0, st>>>(Rn, ldr, cols, K, S, Rq, cols_pad, scale, flags, expect, ctl);
   return cudaGetLastError();
 }
 
 // One K <= 128 block: C += Lq * Rq with the scales of that block.  version 2 (default): resident-A,
 // TMA reduce-add epilogue; the caller has zeroed column slot t beforehand (k_zero_cols).
+// The three tensor maps of a launch depend only on the operand buffers and shapes, which an engine
+// re-uses step after step: encode them once and look them up afterwards (cuTensorMapEncodeTiled is
+// a driver call of several microseconds, three per launch, on a launch-bound path).
+struct Tc05MapKey {
+  const void *Lq, *Rq, *C;
+  int64_t rows_pad, cols_pad, rows, cols, ldc;
+  int S, dev, v1;
+  bool operator==(const Tc05MapKey& o) const { return memcmp(this, &o, sizeof(*this)) == 0; }
+};
+struct Tc05MapEntry {
+  Tc05MapKey key;
+  CUtensorMap tmA, tmB, tmC;
+};
+
 int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
   static const bool use_v1 = getenv("JB_TC05_V1") != nullptr;
+  static std::mutex mu;
+  static std::vector<Tc05MapEntry> cache;
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  Tc05MapKey key;
+  memset(&key, 0, sizeof(key));
+  key.Lq = a.Lq; key.Rq = a.Rq; key.C = a.C; key.rows_pad = a.rows_pad; key.cols_pad = a.cols_pad;
+  key.rows = a.rows; key.cols = a.cols; key.ldc = a.ldc; key.S = a.S; key.dev = cur_dev; key.v1 = use_v1;
   CUtensorMap tmA, tmB, tmC;
-  int rc = make_map_i8(&tmA, a.Lq, (uint64_t)a.rows_pad, (uint64_t)a.S, TC_M);
-  if (rc) return rc;
-  rc = make_map_i8(&tmB, a.Rq, (uint64_t)a.cols_pad, (uint64_t)a.S, use_v1 ? TC_N : V2_N);
-  if (rc) return rc;
+  bool hit = false;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    for (const Tc05MapEntry& en : cache)
+      if (en.key == key) {
+        tmA = en.tmA; tmB = en.tmB; tmC = en.tmC;
+        hit = true;
+        break;
+      }
+  }
+  int rc = JB_OK;
+  if (!hit) {
+    rc = make_map_i8(&tmA, a.Lq, (uint64_t)a.rows_pad, (uint64_t)a.S, TC_M);
+    if (rc) return rc;
+    rc = make_map_i8(&tmB, a.Rq, (uint64_t)a.cols_pad, (uint64_t)a.S, use_v1 ? TC_N : V2_N);
+    if (rc) return rc;
+    memset(&tmC, 0, sizeof(tmC));
+    if (!use_v1 && a.rows >= TC_M && a.cols > 0) {
+      rc = make_map_f64_sw128(&tmC, a.C, (uint64_t)a.cols, (uint64_t)a.rows, (uint64_t)a.ldc);
+      if (rc) return rc;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (cache.size() >= 64) cache.erase(cache.begin());
+    Tc05MapEntry en;
+    en.key = key; en.tmA = tmA; en.tmB = tmB; en.tmC = tmC;
+    cache.push_back(en);
+  }
   Tc05Params P;
   memset(&P, 0, sizeof(P));
   P.C = a.C; P.ldc = a.ldc; P.rscale = a.rscale; P.cscale = a.cscale; P.rows = a.rows; P.cols = a.cols;
@@ -1011,8 +1080,6 @@ int jb_tc05_launch(const Tc05Launch& a, cudaStream_t st) {
     P.ct_count = (int)((a.cols + TC_N - 1) / TC_N);
     k_tc05_update<<<a.grid, TC_THREADS, jb_tc05_smem_bytes(a.S), st>>>(P, tmA, tmB);
   } else {
-    rc = make_map_f64_sw128(&tmC, a.C, (uint64_t)a.cols, (uint64_t)a.rows, (uint64_t)a.ldc);
-    if (rc) return rc;
     P.ct_count = (int)((a.cols + V2_N - 1) / V2_N);
     // column slot t: the v2 epilogue only adds, so the slot is cleared first
     if (a.col_t1 > a.col_t0 && a.zero_slot) {
@@ -1064,7 +1131,8 @@ extern "C" int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t
     JB_CHECK(cudaMemsetAsync(Rq, 0, jb_tc05_rq_bytes(cols_pad, TC_K, S), st));
     JB_CHECK(cudaMemsetAsync(cs, 0, (size_t)cols_pad * 8, st));
     JB_CHECK(jb_tc05_slice_rows(L + k0, ldl, rows, kb, S, Lq, rows, rs, st));
-    JB_CHECK(jb_tc05_slice_cols(Rn + (int64_t)k0 * ldr, ldr, cols, kb, S, Rq, cols_pad, cs, nullptr, 0, st));
+    JB_CHECK(jb_tc05_slice_cols(Rn + (int64_t)k0 * ldr, ldr, cols, kb, S, Rq, cols_pad, cs, nullptr, 0, nullptr,
+                                st));
     Tc05Launch a;
     memset(&a, 0, sizeof(a));
     a.C = C; a.ldc = ldc; a.rows = rows; a.cols = cols; a.Lq = Lq; a.Rq = Rq; a.rows_pad = rows;

@@ -169,6 +169,18 @@ int jb_engine_refine_phase(JbEngine* e, int formula, int phase, void* stream);
 /* stand-alone kernels for tests / tools */
 int jb_block_inverse(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
                      double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
+/* Same operation as jb_block_inverse, for callers that must not allocate (all device memory
+ * already handed to a pool, or no room for cudaMalloc's device-wide synchronisation).  No
+ * counterpart in the reference.  Staging lives in a fixed ~4 MiB device array inside the library
+ * (resident on every GPU that loads it): accepted only if nblocks * Kp * Kp <= 524288 doubles
+ * (Kp = m rounded up to 16) and m <= 256, otherwise JB_ERR_ARG.  Calls no cudaMalloc/cudaFree.
+ * Outputs: d_inv = nblocks packed m x m inverses, d_norms and d_ok = nblocks entries; a singular
+ * block (d_ok = 0) comes back as zeros.  Asynchronous on `stream` (synchronise before reading the
+ * outputs).  All calls on a device share the array: calls that overlap on the GPU race.  The first
+ * call on each device resolves the array's address; make it during initialisation, before any
+ * stream capture begins, and do not reset the device afterwards. */
+int jb_block_inverse_noalloc(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
+                             double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
 /* Message-passing litmus between two peer GPUs of this process (payload stores, fence,
  * st.release.sys flag / ld.acquire.sys spin): counts ordering violations over `iters` epochs. */
 int jb_flag_litmus(int dev_producer, int dev_consumer, int iters, unsigned long long* errors_out);
@@ -176,17 +188,6 @@ int jb_flag_litmus(int dev_producer, int dev_consumer, int iters, unsigned long 
  * tcgen05 int8-split path (K3b) with S slices; rows must be a multiple of 128 (test / tool entry). */
 int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t cols, const double* L,
                         int64_t ldl, const double* Rn, int64_t ldr, int32_t K, int32_t S, void* stream);
-/* Same operation for callers that must not allocate (all device memory already handed to a pool,
- * or no room for cudaMalloc's device-wide synchronisation).  No counterpart in the reference.
- * Staging lives in a fixed ~4 MiB device array inside the library (resident on every GPU that
- * loads it): accepted only if nblocks * Kp * Kp <= 524288 doubles (Kp = m rounded up to 16) and
- * m <= 256, otherwise JB_ERR_ARG.  Calls no cudaMalloc/cudaFree.  Asynchronous on `stream`
- * (synchronise before reading the outputs).  All calls on a device share the array: calls that
- * overlap on the GPU race.  The first call on each device resolves the array's address; make it
- * during initialisation, before any stream capture begins. */
-int jb_block_inverse_noalloc(const double* d_blocks, int64_t nblocks, int32_t m, double norm_a,
-                             double* d_inv, double* d_norms, int32_t* d_ok, void* stream);
-
 #ifdef __cplusplus
 }
 #endif
