@@ -122,7 +122,7 @@ def test_file_input_matches_python_front_end(p, tmp_path):
         for i in range(10):
             for j in range(10):
                 assert abs(got[i][j] - float(want[i, j])) <= 0.006
-    assert res < 1e-10
+    assert res < 1e-9
 
 
 @pytest.mark.parametrize("p", [2, 4, 8])

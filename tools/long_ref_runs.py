@@ -20,7 +20,18 @@ out = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "ref_
 err = rr.ensure_built()
 if err:
     sys.exit(err)
+done = set()
+if os.path.exists(out):
+    for ln in open(out):
+        try:
+            r = json.loads(ln)
+            if r.get("glob_time"):
+                done.add((r["n"], r["m"]))
+        except ValueError:
+            pass
 for n, m, want_res, limit in ((32760, 126, True, 3 * 3600), (32768, 128, False, 6 * 3600)):
+    if (n, m) in done:      # finished in an earlier session
+        continue
     t0 = time.time()
     r = rr.run_once(n, m, 8, timeout_s=limit, want_residual=want_res)
     r.update(n=n, m=m, ranks=8, started=t0, host_cpus=os.cpu_count())
