@@ -94,6 +94,21 @@ __device__ __noinline__ void rowt_item(double* wrow, double* swap_dst, uint32_t*
   }
 }
 
+// B1's early column tiles: every item of the tile (UPD of each row tile, ROWT of block row t) calls
+// this after its stores; the last one flags the tile as carrying step t.  All 4 MMA warps.
+__device__ __forceinline__ void early_arrive(const StepParams& P, const Plan& pl, int epos) {
+  __threadfence();
+  named_bar_sync(1, MMA_WARPS * 32);
+  if (threadIdx.x == 0) {
+    const uint32_t want = (uint32_t)(pl.rtu + (P.t_slot >= 0 ? P.nsub : 0));
+    const uint32_t old = atomicAdd(P.early + epos, 1u);
+    if (old == want - 1) {
+      P.early[epos] = 0;
+      st_release_sys_u32(P.early + 8 + epos, P.tag);
+    }
+  }
+}
+
 // One thread per retiring CTA of phase B1; the last one publishes "B1(t) done".
 __device__ __forceinline__ void b1_retire(const StepParams& P) {
   const uint32_t old = atomicAdd(P.b1sync, 1u);
@@ -295,6 +310,13 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
                 (P.b1sync && P.t >= 2) ? P.stepdone_peers[P.rank] + si.piv_rank : nullptr, P.tag - 2,
                 rowbuf_local + roff, rowflag_local + it.ct, P.row_expect, P.tag, it.rows_valid, ncol,
                 P.ldw, abort_flag, spin_to);
+      // B1's early column tiles: block row t is part of "this tile carries step t" - phase A of the
+      // next step updates row t as an ordinary row and K1(t+2) copies it into the L panel - so the
+      // install counts towards the tile's flag like the UPD items do
+      if (!kScale && P.phase == JB_PHASE_B1) {
+        const int epos = np_pos(P, pl, it.ct);
+        if (epos < P.nearly) early_arrive(P, pl, epos);
+      }
       continue;
     }
 
@@ -384,17 +406,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         named_bar_sync(1, MMA_WARPS * 32);
         if (tid == 0) st_release_sys_u32(P.prowflag + it.ct * P.nsub + it.sub, P.tag);
       }
-      if (kRowt && !kScale && it.epos >= 0) {  // B1's early column tiles: the last item flags the tile
-        __threadfence();
-        named_bar_sync(1, MMA_WARPS * 32);
-        if (tid == 0) {
-          const uint32_t old = atomicAdd(P.early + it.epos, 1u);
-          if (old == (uint32_t)pl.rtu - 1) {
-            P.early[it.epos] = 0;
-            st_release_sys_u32(P.early + 8 + it.epos, P.tag);
-          }
-        }
-      }
+      if (kRowt && !kScale && it.epos >= 0) early_arrive(P, pl, it.epos);  // B1's early column tiles
     } else if (kScale) {
       // SCALE: column slot t of the pivot row is P^-1 itself; broadcast the tile to all ranks
       const double* pinv = P.invbuf + (int64_t)sc_slot * P.Kp * P.Kp;
