@@ -85,3 +85,53 @@ extern "C" int jb_flag_litmus(int dev_producer, int dev_consumer, int iters,
   cudaFree(ack);
   return JB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Store bandwidth of the paths the SCALE items use to hand the pivot row to the other GPUs
+// (measured NVLink roof for profiles/): 16-byte stores to a peer-mapped address, or multimem.st to
+// the NVLS multicast alias.  mode 0: st.global.v2.f64 (dst may be local or a peer mapping),
+// mode 1: multimem.st (dst = multicast alias), mode 2: ld.global.v2.f64 (peer pull).
+__global__ void __launch_bounds__(256) k_store_bw(double* dst, size_t n_pairs, int mode, double* sink) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  double acc = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs; i += stride) {
+    double* p = dst + 2 * i;
+    if (mode == 0) {
+      *reinterpret_cast<double2*>(p) = make_double2((double)i, 1.0);
+    } else if (mode == 1) {
+      jb::multimem_st_v2f64(p, (double)i, 1.0);
+    } else {
+      const double2 v = *reinterpret_cast<const double2*>(p);
+      acc += v.x + v.y;
+    }
+  }
+  if (mode == 2 && acc == 123.456) *sink = acc;  // keep the loads
+}
+
+// Returns the average milliseconds of `iters` launches over `bytes` (after one warm-up launch).
+extern "C" int jb_store_bandwidth(void* dst, size_t bytes, int mode, int iters, float* ms_out) {
+  if (!dst || bytes < 16 || iters < 1 || mode < 0 || mode > 2 || !ms_out) {
+    jb_set_error("jb_store_bandwidth: bad arguments");
+    return JB_ERR_ARG;
+  }
+  double* sink = nullptr;
+  JB_CHECK(cudaMalloc((void**)&sink, 8));
+  cudaEvent_t e0, e1;
+  JB_CHECK(cudaEventCreate(&e0));
+  JB_CHECK(cudaEventCreate(&e1));
+  const size_t pairs = bytes / 16;
+  k_store_bw<<<148 * 8, 256>>>((double*)dst, pairs, mode, sink);
+  JB_CHECK(cudaDeviceSynchronize());
+  JB_CHECK(cudaEventRecord(e0));
+  for (int i = 0; i < iters; ++i) k_store_bw<<<148 * 8, 256>>>((double*)dst, pairs, mode, sink);
+  JB_CHECK(cudaEventRecord(e1));
+  JB_CHECK(cudaEventSynchronize(e1));
+  JB_CHECK(cudaGetLastError());
+  float ms = 0;
+  JB_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+  *ms_out = ms / iters;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(sink);
+  return JB_OK;
+}

@@ -184,6 +184,10 @@ int jb_block_inverse_noalloc(const double* d_blocks, int64_t nblocks, int32_t m,
 /* Message-passing litmus between two peer GPUs of this process (payload stores, fence,
  * st.release.sys flag / ld.acquire.sys spin): counts ordering violations over `iters` epochs. */
 int jb_flag_litmus(int dev_producer, int dev_consumer, int iters, unsigned long long* errors_out);
+/* Store / load bandwidth of the paths the broadcast uses (tools/nvlink_bw.py): mode 0 = 16-byte
+ * stores to dst (local or peer mapping), 1 = multimem.st to an NVLS multicast alias, 2 = 16-byte
+ * loads.  ms_out = average milliseconds per pass over `bytes`.  No counterpart in the reference. */
+int jb_store_bandwidth(void* dst, size_t bytes, int mode, int iters, float* ms_out);
 /* C (rows x cols) += L (rows x K) * Rn (K x cols), fp64 operands in device memory, computed on the
  * tcgen05 int8-split path (K3b) with S slices; rows must be a multiple of 128 (test / tool entry). */
 int jb_tc05_gemm_update(double* C, int64_t ldc, int64_t rows, int64_t cols, const double* L,

@@ -128,56 +128,19 @@ class JordanSolver:
         self.comm.barrier()
 
     def _try_native_heap(self) -> bool:
-        lib, comm, p = self.lib, self.comm, self.comm.world
-        all_ok = lambda flag: comm.allreduce_sum_int(1 if flag else 0) == p  # noqa: E731
-        heap, fd = C.c_void_p(), C.c_int(-1)
-        nbytes = int(lib.jb_engine_symm_bytes(self._h))
-        want_mc = 0 if os.environ.get("JB_NO_MULTICAST") else 1
-        rc = lib.jb_symm_heap_create(nbytes, self.device, comm.rank, p, want_mc, C.byref(heap), C.byref(fd))
-        if not all_ok(rc == 0):
-            self._symm_err = lib.jb_last_error().decode(errors="replace")
-            if rc == 0:
-                os.close(fd.value)
-                lib.jb_symm_heap_destroy(heap)
+        from ..parallel.symm import NativeSymmHeap
+
+        p = self.comm.world
+        heap = NativeSymmHeap.create(self.comm, int(self.lib.jb_engine_symm_bytes(self._h)), self.device,
+                                     want_multicast=not os.environ.get("JB_NO_MULTICAST"))
+        if heap is None:
+            self._symm_err = NativeSymmHeap.last_error
             return False
-        self._symm_serial = getattr(JordanSolver, "_symm_serial", 0) + 1
-        JordanSolver._symm_serial = self._symm_serial
-        fds = comm.exchange_fds(fd.value, tag=f"h{self._symm_serial}")
-        os.close(fd.value)
-        arr = (C.c_int * p)(*fds)
-        arr[comm.rank] = -1
-        rc = lib.jb_symm_heap_import(heap, arr)
-        if not all_ok(rc == 0):
-            self._symm_err = lib.jb_last_error().decode(errors="replace")
-            lib.jb_symm_heap_destroy(heap)
-            return False
-        mc = all_ok(bool(lib.jb_symm_heap_multicast_supported(heap)))
-        if mc:
-            mfd = C.c_int(-1)
-            ok0 = True
-            if comm.rank == 0:
-                ok0 = lib.jb_symm_heap_mc_create(heap, C.byref(mfd)) == 0
-            if all_ok(ok0):
-                got = comm.bcast_fd(mfd.value, src=0, tag=f"m{self._symm_serial}")
-                ok = True
-                if comm.rank == 0:
-                    os.close(mfd.value)
-                else:
-                    ok = lib.jb_symm_heap_mc_import(heap, got) == 0
-                ok = all_ok(ok)
-                ok = ok and all_ok(lib.jb_symm_heap_mc_add(heap) == 0)     # vote = barrier: all added
-                ok = ok and all_ok(lib.jb_symm_heap_mc_bind(heap) == 0)    # vote = barrier: all bound
-                mc = ok
-            else:
-                mc = False
-            if not mc:
-                lib.jb_symm_heap_mc_drop(heap)
-        ptrs = (C.c_void_p * p)(*[C.c_void_p(lib.jb_symm_heap_ptr(heap, r)) for r in range(p)])
-        mcp = lib.jb_symm_heap_mc_ptr(heap) if mc else None
-        _native.check(lib.jb_engine_bind_symm(self._h, ptrs, C.c_void_p(mcp or 0)))
+        ptrs = (C.c_void_p * p)(*[C.c_void_p(x) for x in heap.ptrs])
+        _native.check(self.lib.jb_engine_bind_symm(self._h, ptrs, C.c_void_p(heap.mc_ptr)))
         self._heap = heap
-        self.multicast = bool(mc)
-        self.symm_mode = "vmm" + ("+nvls" if mc else "")
+        self.multicast = heap.mc_ptr != 0
+        self.symm_mode = "vmm" + ("+nvls" if heap.mc_ptr else "")
         return True
 
     def _try_torch_symm(self) -> bool:
@@ -382,7 +345,7 @@ class JordanSolver:
             self.lib.jb_engine_destroy(self._h)
             self._h = None
             if getattr(self, "_heap", None):
-                self.lib.jb_symm_heap_destroy(self._heap)   # the heap outlives the engine bound to it
+                self._heap.close()   # the heap outlives the engine bound to it
                 self._heap = None
 
     def __del__(self):  # pragma: no cover
