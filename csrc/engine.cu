@@ -89,7 +89,11 @@ struct JbEngine {
   bool lookahead = true;
   bool k1_early = true;    // K1(t+2) pending right behind A(t+1) (JB_K1_GATED=1: released by the end of B2(t))
   int sched = 0;           // JB_SCHED: 1 = phase A in line (between B2(t-1) and B1(t)), else A beside B2(t-1)
-  bool b2_overlap = true;  // B2 on its own stream (moves in while B1 drains); JB_B2_SERIAL=1: behind B1
+  // B2(t) starts behind B1(t).  Letting it move in while B1 drains (JB_B2_OVERLAP=1: no event wait,
+  // only the per-tile flags) measured no gain (0.3099 s against 0.3084-0.3123 s at 8 GPUs) and gave
+  // WRONG inverses at 8 GPUs, n = 32768 (residual 1e11; 2 GPUs were fine), cause not found: the
+  // switch is kept for debugging only.
+  bool b2_overlap = false;
   // tcgen05 split-precision update (precision = 1)
   bool tc05 = false;
   int tc_slices = 8;
@@ -268,7 +272,7 @@ int jb_engine_create(const JbConfig* cfg, JbEngine** out) {
   if (const char* f = getenv("JB_B1_FRAC")) e->b1_frac = std::max(0.0, std::min(1.0, atof(f)));
   if (getenv("JB_TIME_KERNELS")) e->profile = true;
   if (getenv("JB_NO_LOOKAHEAD")) e->lookahead = false;
-  if (getenv("JB_B2_SERIAL")) e->b2_overlap = false;
+  if (getenv("JB_B2_OVERLAP")) e->b2_overlap = true;
   if (getenv("JB_K1_GATED")) e->k1_early = false;
   if (const char* sc = getenv("JB_SCHED")) e->sched = atoi(sc);
   {
@@ -665,9 +669,8 @@ int jb_engine_invert(JbEngine* e, void* stream) {
   // Three streams, per step t:
   //   caller's stream : B1(t)   ROWT(t) of the non-priority tiles + UPD(t) of the first few of them
   //                             (starting with block column t+2, flagged when done)
-  //   bstream         : B2(t)   launched when K1(t+1) has finished; its CTAs move in while B1(t)
-  //                             drains.  Next pivot row first (UPDP), SCALE(t+1) -> broadcast for
-  //                             step t+1, then the bulk of UPD(t)
+  //   bstream         : B2(t)   launched when K1(t+1) and B1(t) have finished.  Next pivot row first
+  //                             (UPDP), SCALE(t+1) -> broadcast for step t+1, then the bulk of UPD(t)
   //   hstream (high)  : A(t+1)  launched together with B2(t) on a small grid: ROWT(t+1) + UPD(t+1)
   //                             of block columns t+1, t+2 as soon as their pivot-row tiles land;
   //                     K1(t+2) right behind it: pending at high priority, so its CTAs (which need
@@ -703,7 +706,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       JB_CHECK(cudaEventRecord(e->evB1[t & 1], st));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 4], st));
       JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evK[(t + 1) & 1], 0));
-      if (!e->b2_overlap) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[t & 1], 0));  // JB_B2_SERIAL
+      if (!e->b2_overlap) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[t & 1], 0));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 5], e->bstream));
       JB_CHECK(launch_step(t, JB_PHASE_B2, e->bstream, grid));
       JB_CHECK(cudaEventRecord(e->evB2[t & 1], e->bstream));
@@ -743,7 +746,7 @@ int jb_engine_invert(JbEngine* e, void* stream) {
       // B2(t): needs pivot(t+1); B1(t-1) is long finished (explicit only for the record)
       JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evK[(t + 1) & 1], 0));
       if (t > 0) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[(t + 1) & 1], 0));
-      if (!e->b2_overlap) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[t & 1], 0));  // JB_B2_SERIAL
+      if (!e->b2_overlap) JB_CHECK(cudaStreamWaitEvent(e->bstream, e->evB1[t & 1], 0));
       JB_CHECK(cudaEventRecord(e->evG[t & 1], e->bstream));
       if (e->profile) JB_CHECK(cudaEventRecord(e->ev[8 * t + 5], e->bstream));
       JB_CHECK(launch_step(t, JB_PHASE_B2, e->bstream, grid));
