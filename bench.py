@@ -25,6 +25,13 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "fp64_inverse_gflops"
+# the unmodified reference at the headline config (n = 32768, m = 128, 8 MPI ranks
+# on the 8-core build box): glob_time 4719.7 s -> 2 n^3 / t.  At its best block size (m = 126,
+# n = 32760) it needs 535.86 s.  The reference publishes no numbers of its own.
+REF_HEADLINE = {"n": 32768, "m": 128, "ranks": 8, "glob_time_s": 4719.7, "gflops": 2.0 * 32768.0 ** 3 / 4719.7 / 1e9,
+                "best_block_size": {"n": 32760, "m": 126, "glob_time_s": 535.86,
+                                    "gflops": 2.0 * 32760.0 ** 3 / 535.86 / 1e9, "residual": 2.113970e-04},
+                "source": "BASELINE.md section 4, profiles/ref_long_runs.jsonl (host CPUs; the reference has no GPU path)"}
 
 
 def parse_args():
@@ -153,12 +160,17 @@ def run_own(args) -> dict:
     out = {
         "metric": METRIC, "value": value, "unit": "GFLOP/s", "n_gpus": comm.world, "steps": K,
         "warmup": W, "ms_per_step": ms, "seconds_per_inversion": ms * 1e-3, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "fp64", "data": "synthetic",
+        "scaling": "strong",
+        "vs_baseline": (value / REF_HEADLINE["gflops"]) if (n == REF_HEADLINE["n"] and m == REF_HEADLINE["m"]) else None,
+        "baseline_number": REF_HEADLINE, "dtype": "fp64", "data": "synthetic",
         "impl": "own",
         "config": {"model": "block Gauss-Jordan inverse, generator |i-j|", "n": n, "m": m,
                    "global_batch": 1, "seq_len": n, "parallelism": f"block-cyclic rows x{comm.world}",
                    "flop_convention": "2n^3 (executed)", "symm": s.symm_mode, "update_path": args.precision,
-                   "l2": "inputs (n^2*8 B per inversion) larger than L2; matrix regenerated every step"},
+                   "l2": "inputs (n^2*8 B per inversion) larger than L2; matrix regenerated every step",
+                   "note": "vs_baseline divides by the unmodified reference at the same n and m (8 host ranks, "
+                           "14.9 GFLOP/s); at its best nearby block size (m = 126) the reference reaches 131 GFLOP/s "
+                           "(SURVEY D11: its 3x3-blocked path needs block sizes divisible by 3)"},
         "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": t_wall / max(K, 1) * 1e3,
         "invert_only": {"ms_per_step": inv_ms, "value": flops(n) / (inv_ms * 1e-3) / 1e9, "unit": "GFLOP/s",
                         "note": "CUDA events around the Nr elimination steps only (the reference's glob_time "

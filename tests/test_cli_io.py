@@ -145,3 +145,19 @@ def test_reference_bench_arm_line(reference):
     d = json.loads(r.stdout.strip().splitlines()[-1])
     assert d["impl"] == "reference" and d["metric"] == "fp64_inverse_gflops" and d["n_gpus"] == 2
     assert d["config"]["n"] == 600 and d["value"] > 0 and d["gpu_launches"] == 0
+    # end to end for the reference = job launch -> glob_time line; it can only be slower than Jordan alone
+    assert d["e2e"]["unit"] == "GFLOP/s" and 0 < d["e2e"]["value"] <= d["value"] * 1.01
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+
+
+def test_reference_bench_arm_quotes_best_block_size(reference):
+    """m = 64 is off the reference's 3x3-blocked fast path: the arm also reports m = 63."""
+    import json
+
+    env = dict(os.environ, JB_REF_BUDGET_S="30")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+                        "--n", "640", "--m", "64"], capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    best = d["reference_best_block_size"]
+    assert best["m"] == 63 and best["n"] % 63 == 0 and best["value"] > 0
