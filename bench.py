@@ -180,38 +180,46 @@ def run_own(args) -> dict:
     }
     if residual is not None:
         out["residual"] = residual
+        # ||AX - I||inf of the LAST timed inversion, computed after the timed region; the reference
+        # reaches 2.1e-04 at this size - anything far above means a wrong inverse
+        out["residual_ok"] = bool(residual == residual and residual < 1e-2)
     s.close()
     if not args.no_checks:
-        out["ref_config_check"] = ref_config_check(args, comm, local_rank)
-        out["pivoting_check"] = pivoting_check(args, comm, local_rank)
+        # after the timed region; a failure here must never cost the headline line
+        for key, fn in (("ref_config_check", ref_config_check), ("pivoting_check", pivoting_check)):
+            try:
+                out[key] = fn(args, comm, local_rank)
+            except Exception as exc:  # noqa: BLE001
+                out[key] = {"error": repr(exc)[:300]}
     # ---------------------------------------------------------------- second arm: tcgen05 update path
     # Same inversion with the trailing update on tcgen05.mma kind::i8 (error-free int8 split, exact
     # int32 accumulation in TMEM).  Reported next to the headline, never instead of it: the headline
     # `value` stays the native-fp64 (DMMA) path.
     if args.precision == "fp64" and m % 128 == 0 and m <= 256 and not args.no_alt:
-        s2 = JordanSolver(n, m, comm=comm, device=local_rank, precision="tc05")
-        s2.fill_formula(args.formula)
-        s2.invert_async()
-        s2.status()
-        torch.cuda.synchronize()
-        comm.barrier()
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record()
-        for _ in range(2):
+        try:
+            s2 = JordanSolver(n, m, comm=comm, device=local_rank, precision="tc05")
             s2.fill_formula(args.formula)
             s2.invert_async()
             s2.status()
-        a1.record()
-        torch.cuda.synchronize()
-        ms2 = comm.allreduce_max(a0.elapsed_time(a1)) / 2
-        res2 = s2.residual()
-        out["alt_paths"] = {"tcgen05_int8_split": {
-            "value": flops(n) / (ms2 * 1e-3) / 1e9, "unit": "GFLOP/s (fp64-equivalent, 2n^3)", "ms_per_step": ms2,
-            "residual": res2, "slices": int(os.environ.get("JB_TC05_SLICES", "8")),
-            "note": "exact int32 accumulation of 7-bit slices; residual is at fp64 level (compare `residual_fp64_path`)"}}
-        if residual is None:
-            pass
-        s2.close()
+            torch.cuda.synchronize()
+            comm.barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(2):
+                s2.fill_formula(args.formula)
+                s2.invert_async()
+                s2.status()
+            a1.record()
+            torch.cuda.synchronize()
+            ms2 = comm.allreduce_max(a0.elapsed_time(a1)) / 2
+            res2 = s2.residual()
+            out["alt_paths"] = {"tcgen05_int8_split": {
+                "value": flops(n) / (ms2 * 1e-3) / 1e9, "unit": "GFLOP/s (fp64-equivalent, 2n^3)", "ms_per_step": ms2,
+                "residual": res2, "slices": int(os.environ.get("JB_TC05_SLICES", "8")),
+                "note": "exact int32 accumulation of 7-bit slices; residual is at fp64 level (compare `residual_fp64_path`)"}}
+            s2.close()
+        except Exception as exc:  # noqa: BLE001 - the second arm must never cost the headline line
+            out["alt_paths"] = {"tcgen05_int8_split": {"error": repr(exc)[:300]}}
     return out if comm.rank == 0 else {}
 
 
