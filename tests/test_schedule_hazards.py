@@ -36,3 +36,25 @@ def test_model_finds_the_uncounted_row_install():
     assert ScheduleModel(8, 3, count_rowt_in_early=False).hazards() == []
     hz = ScheduleModel(8, 3, count_rowt_in_early=False, b2_overlap=True).hazards()
     assert hz and all("ROWT" in h for h in hz)
+
+
+@pytest.mark.parametrize("Nr,p,seed", [(8, 2, 1), (9, 3, 2), (12, 4, 3), (16, 8, 4), (12, 4, 5), (10, 1, 6)])
+@pytest.mark.parametrize("kw", [dict(), dict(sched=1)])
+def test_block_row_swaps_are_ordered_too(Nr, p, seed, kw):
+    """Random pivot sequences off the diagonal: pushes of the old row t into the pivot owner's swap
+    buffer (peer stores + swap flags), update of the swapped-in row from that buffer, next pivot row
+    that is itself a swapped-in row - all conflicting accesses ordered."""
+    import random
+
+    rnd = random.Random(seed)
+    piv = [rnd.choice([t, rnd.randrange(t, Nr)]) for t in range(Nr)]
+    assert ScheduleModel(Nr, p, pivots=piv, **kw).hazards() == []
+
+
+def test_model_finds_the_unguarded_swap_push():
+    """Two swaps of the same buffer parity onto one pivot owner: without waiting for that owner's
+    step-retired tag the second push may overwrite rows the owner still reads for the first swap."""
+    piv = [4, 1, 8, 3, 4, 5, 6, 7, 8, 9, 10, 11]
+    assert ScheduleModel(12, 4, pivots=piv).hazards() == []
+    hz = ScheduleModel(12, 4, pivots=piv, swap_handshake=False).hazards()
+    assert hz and all("swapbuf" in h and "push" in h for h in hz)

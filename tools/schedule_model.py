@@ -18,8 +18,8 @@ accesses (same buffer tile, at least one write) is ordered:
 The host-side launch sequence below mirrors jb_engine_invert (csrc/engine.cu), including its
 switches (sched: 2 = phase A beside B2, 1 = in line; b2_overlap; k1_gated).  A hazard reported here
 is a possible race on the GPU whatever the timing; no report means the model found every conflicting
-pair ordered.  Diagonal pivots only (no block-row swaps): the swap path is covered by the oracle
-tests on the GPU.
+pair ordered.  Pivot sequences may leave the diagonal: the block-row swap (peer stores into the pivot
+owner's swap buffer, swap flags, update of the swapped-in row from that buffer) is part of the model.
 """
 from __future__ import annotations
 
@@ -77,21 +77,27 @@ class Stream:
         return v
 
 
-def _enumerate(m, p, rank, rloc, ldw, t, phase, pct0, pct1, nb1, nearly, next_rank, next_slot):
+def _enumerate(m, p, rank, rloc, ldw, t, piv_g, phase, pct0, pct1, nb1, nearly, next_rank, next_slot):
     cap = 1 << 16
     buf = (C.c_int32 * (5 * cap))()
-    n = _native.host().jb_plan_enumerate(m, p, rank, rloc, ldw, t, t % p, t // p, 0, phase, pct0, pct1, nb1, nearly,
-                                         next_rank, next_slot, buf, cap)
+    n = _native.host().jb_plan_enumerate(m, p, rank, rloc, ldw, t, piv_g % p, piv_g // p, int(piv_g != t), phase,
+                                         pct0, pct1, nb1, nearly, next_rank, next_slot, buf, cap)
     assert n >= 0
     return [tuple(buf[5 * i + k] for k in range(5)) for i in range(n)]
 
 
 class ScheduleModel:
-    """Nr block rows of size m = 128 over p ranks, diagonal pivots."""
+    """Nr block rows of size m = 128 over p ranks.  pivots[t] = global block row chosen at step t
+    (>= t; default: the diagonal).  A pivot off the diagonal adds the block-row swap: ROWT pushes the
+    old row t into the pivot owner's swap buffer, the swapped-in row is updated from there."""
 
     def __init__(self, Nr: int, p: int, sched: int = 2, b2_overlap: bool = False, k1_gated: bool = False,
-                 frac: float = 0.3, count_rowt_in_early: bool = True, stepdone_handshake: bool = True):
+                 frac: float = 0.3, count_rowt_in_early: bool = True, stepdone_handshake: bool = True,
+                 pivots=None, swap_handshake: bool = True):
         self.Nr, self.p, self.m = Nr, p, 128
+        self.swap_handshake = swap_handshake
+        self.pivots = list(pivots) if pivots is not None else list(range(Nr))
+        assert len(self.pivots) == Nr and all(t <= g < Nr for t, g in enumerate(self.pivots))
         self.sched, self.b2_overlap, self.k1_gated, self.frac = sched, b2_overlap, k1_gated, frac
         self.count_rowt_in_early, self.stepdone_handshake = count_rowt_in_early, stepdone_handshake
         self.CT = Nr                       # m == BN: one column tile per block column
@@ -147,17 +153,63 @@ class ScheduleModel:
         self._access(("stepinfo", r, t), s, e, True, lab)
         return e
 
+    def _row_item(self, r, t, name, ks, ty, ct, lrow0, prow, wait_prev_early):
+        """ROWT / UPD / UPD_SWAPPED item of step t; returns (end node, is ROWT)."""
+        g, p, m = self.g, self.p, self.m
+        piv_g = self.pivots[t]
+        piv_rank, piv_slot, do_swap = piv_g % p, piv_g // p, piv_g != t
+        slot, sub = lrow0 // m, (lrow0 % m) // 64
+        kind = {ROWT: "ROWT", UPD: "UPDP" if prow else "UPD", UPD_SW: "UPDSW"}[ty]
+        lab = f"r{r} {name}({t}) {kind} slot{slot} sub{sub} ct{ct}"
+        s = g.node(lab + " start", ks)
+        if wait_prev_early is not None:
+            self.waits.append((s, wait_prev_early))
+        tile_t = (t * m) // BN                      # column tile holding block column t (m == BN)
+        if ty == ROWT:
+            cur = s
+            if do_swap:                             # push the old row t to the pivot owner (main.cpp:1100-1131)
+                if t >= 2 and self.stepdone_handshake and self.swap_handshake:
+                    self.waits.append((s, ("stepdone", piv_rank, t - 2)))
+                mid = g.node(lab + " pushed", s)
+                self._access(("W", r, slot, sub, ct), s, mid, False, lab + " push")
+                self._access(("swapbuf", piv_rank, t & 1, ct, sub), s, mid, True, lab + " push")
+                self._publish(("swapflag", t, ct, sub), mid)
+                cur = mid
+            s2 = g.node(lab + " install", cur)
+            self.waits.append((s2, ("rowflag", t, ct)))
+            e = g.node(lab + " end", s2)
+            self._access(("stepinfo", r, t), s, e, False, lab)
+            self._access(("rowbuf", r, t & 1, ct, sub), s2, e, False, lab)
+            self._access(("W", r, slot, sub, ct), s2, e, True, lab)
+            return e, True
+        e = g.node(lab + " end", s)
+        self.waits.append((s, ("rowflag", t, ct)))
+        self._access(("stepinfo", r, t), s, e, False, lab)
+        for sb in range(self.nsub):
+            self._access(("rowbuf", r, t & 1, ct, sb), s, e, False, lab)
+        if ty == UPD_SW:
+            assert do_swap and r == piv_rank and slot == piv_slot
+            for c in {tile_t, ct}:
+                self.waits.append((s, ("swapflag", t, c, sub)))
+                self._access(("swapbuf", r, t & 1, c, sub), s, e, False, lab)
+        else:
+            self._access(("Lbuf", r, t % 3), s, e, False, lab)
+            self._access(("W", r, slot, sub, ct), s, e, False, lab)
+        self._access(("W", r, slot, sub, ct), s, e, True, lab)
+        if prow:
+            self._publish(("prow", r, t, ct, sub), e)
+        return e, False
+
     def _step_kernel(self, stream: Stream, r: int, t: int, phase: int, last=False, *preds):
         """One launch of k_step_fused; returns its end node."""
         g, p, m = self.g, self.p, self.m
         pct0, pct1, nnp, nearly, nb1 = self.split(t, last)
-        nxt = t + 1 if (phase == PH_B2 and t + 1 < self.Nr) else -1
-        items = _enumerate(m, p, r, self.rloc(r), self.ldw, t, phase, pct0, pct1, nb1, nearly,
+        nxt = self.pivots[t + 1] if (phase == PH_B2 and t + 1 < self.Nr) else -1
+        items = _enumerate(m, p, r, self.rloc(r), self.ldw, t, self.pivots[t], phase, pct0, pct1, nb1, nearly,
                            nxt % p if nxt >= 0 else -1, nxt // p if nxt >= 0 else 0)
         name = {PH_A: "A", PH_S: "S", PH_B1: "B1", PH_B2: "B2"}[phase]
         ks = stream.op(f"r{r} {name}({t}) start", *preds)
         ends = []
-        t_slot = t // p if t % p == r else -1
         c0 = nb1 if phase == PH_B2 else 0
         early_items = defaultdict(list)
         for (ty, ct, lrow0, rows, prow) in items:
@@ -180,7 +232,8 @@ class ScheduleModel:
                             self.waits.append((s, ("early", r, t, pos)))
                         else:
                             self.waits.append((s, ("b1done", r, t)))
-                pslot = st // p
+                assert self.pivots[st] % p == r
+                pslot = self.pivots[st] // p
                 for sb in range(self.nsub):
                     self._access(("W", r, pslot, sb, ct), s, e, False, lab)
                 self._access(("invbuf", r, st & 1), s, e, False, lab)
@@ -189,12 +242,7 @@ class ScheduleModel:
                     self._access(("rowbuf", q, st & 1, ct, sub), s, e, True, lab)
                 self._publish(("rowflag", st, ct), e)
             else:
-                slot, sub = lrow0 // m, (lrow0 % m) // 64
-                kind = "ROWT" if ty == ROWT else ("UPDP" if prow else "UPD")
-                lab = f"r{r} {name}({t}) {kind} slot{slot} sub{sub} ct{ct}"
-                s = g.node(lab + " start", ks)
-                e = g.node(lab + " end", s)
-                self.waits.append((s, ("rowflag", t, ct)))
+                prev_early = None
                 if phase == PH_A and t > 0:
                     ppct0, ppct1 = self.pri(t - 1)
                     if ct < ppct0 or ct > ppct1:
@@ -202,21 +250,11 @@ class ScheduleModel:
                         if j < 0:
                             j += self.CT
                         if j < 8:
-                            self.waits.append((s, ("early", r, t - 1, j)))
-                self._access(("stepinfo", r, t), s, e, False, lab)
-                if ty == ROWT:
-                    self._access(("rowbuf", r, t & 1, ct, sub), s, e, False, lab)
-                    self._access(("W", r, slot, sub, ct), s, e, True, lab)
-                else:
-                    for sb in range(self.nsub):
-                        self._access(("rowbuf", r, t & 1, ct, sb), s, e, False, lab)
-                    self._access(("Lbuf", r, t % 3), s, e, False, lab)
-                    self._access(("W", r, slot, sub, ct), s, e, True, lab)
-                    if prow:
-                        self._publish(("prow", r, t, ct, sub), e)
+                            prev_early = ("early", r, t - 1, j)
+                e, is_rowt = self._row_item(r, t, name, ks, ty, ct, lrow0, prow, prev_early)
                 if phase == PH_B1 and not (pct0 <= ct <= pct1):
                     pos = self.np_pos(t, ct)
-                    if pos < nearly and (ty != ROWT or self.count_rowt_in_early):
+                    if pos < nearly and (not is_rowt or self.count_rowt_in_early):
                         early_items[pos].append(e)
             ends.append(e)
         ke = stream.op(f"r{r} {name}({t}) end", *ends)
@@ -305,25 +343,10 @@ class ScheduleModel:
 
     def _wide_last(self, stream, r, t):
         """Last step of the in-line schedule: phase A over every column tile (ROWT + UPD of everything)."""
-        g, p, m = self.g, self.p, self.m
-        items = _enumerate(m, p, r, self.rloc(r), self.ldw, t, PH_A, 0, self.CT - 1, 0, 0, -1, 0)
+        items = _enumerate(self.m, self.p, r, self.rloc(r), self.ldw, t, self.pivots[t], PH_A, 0, self.CT - 1, 0, 0,
+                           -1, 0)
         ks = stream.op(f"r{r} Awide({t}) start")
-        ends = []
-        for (ty, ct, lrow0, rows, prow) in items:
-            slot, sub = lrow0 // m, (lrow0 % m) // 64
-            lab = f"r{r} Awide({t}) {'ROWT' if ty == ROWT else 'UPD'} slot{slot} sub{sub} ct{ct}"
-            s = g.node(lab + " start", ks)
-            e = g.node(lab + " end", s)
-            self.waits.append((s, ("rowflag", t, ct)))
-            self._access(("stepinfo", r, t), s, e, False, lab)
-            if ty == ROWT:
-                self._access(("rowbuf", r, t & 1, ct, sub), s, e, False, lab)
-            else:
-                for sb in range(self.nsub):
-                    self._access(("rowbuf", r, t & 1, ct, sb), s, e, False, lab)
-                self._access(("Lbuf", r, t % 3), s, e, False, lab)
-            self._access(("W", r, slot, sub, ct), s, e, True, lab)
-            ends.append(e)
+        ends = [self._row_item(r, t, "Awide", ks, ty, ct, lrow0, prow, None)[0] for (ty, ct, lrow0, rows, prow) in items]
         stream.op(f"r{r} Awide({t}) end", *ends)
 
     # ------------------------------------------------------------------ cross-rank edges + check
@@ -348,7 +371,7 @@ class ScheduleModel:
             writes = [x for x in lst if x[2]]
             for w in writes:
                 for o in lst:
-                    if o is w or (o[2] and id(o) < id(w)):
+                    if o is w or o[0] == w[0] or (o[2] and id(o) < id(w)):   # same item / pair seen from the other side
                         continue
                     if self.before(w[1], o[0]) or self.before(o[1], w[0]):
                         continue
