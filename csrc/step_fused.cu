@@ -232,7 +232,7 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
           // SCALE(t+1) reads the next pivot row as left by UPD(t).  The tiles of THIS phase are the
           // UPDP items at the head of the work list (lower claim index, hence running): wait for
           // their flags.  Priority tiles were finished by phase A (an earlier launch on the way to
-          // K1(t+1)).  The rest belongs to phase B1, which may still be running beside us but never
+          // K1(t+1)).  The rest belongs to phase B1, which (JB_B2_OVERLAP only) may still be running but never
           // waits for this launch: its first `nearly` tiles are flagged one by one, for the others
           // wait until its last CTA has retired.
           if (!peers_done && P.t > 0) {

@@ -50,7 +50,8 @@ struct Plan {
 //         it on a high-priority stream.  The non-priority tiles are visited cyclically starting
 //         right behind the priority range, so B1 begins with the tiles of block column t+2 - the
 //         ones phase A of the NEXT step needs; B1 flags each of these `nearly` tiles when done.
-//   B2  : launched once K1(t+1) has chosen the next pivot row; runs beside the tail of B1.  On the
+//   B2  : launched once K1(t+1) has chosen the next pivot row and B1 has finished (or, with the
+//         debugging switch JB_B2_OVERLAP, beside the tail of B1: hence the flags below).  On the
 //         owner of that row: UPD(t) of the row's tiles of this phase first (UPDP); then SCALE(t+1)
 //         straight into all ranks' pivot-row buffers of step t+1 - the broadcast of step t+1
 //         overlaps the bulk of step t - in this order: priority tiles, B1's early tiles (flagged),

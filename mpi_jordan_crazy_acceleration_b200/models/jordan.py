@@ -330,7 +330,7 @@ class JordanSolver:
                     "lookahead": False}
         # look-ahead: kernel durations (they overlap, so they do not add up to the inversion time) of
         # A(t) (swap + block columns t, t+1; beside B2(t-1)), B1(t), B2(t) (next pivot row scaled +
-        # broadcast, rest of the update; moves in while B1 drains) and K1(t+1) incl. its wait for SMs
+        # broadcast, rest of the update) and K1(t+1) incl. its wait for SMs
         return {"stepA_ms": seg[0], "stepB1_ms": seg[1], "stepB2_ms": seg[2], "k1_ms": seg[3],
                 "tail_ms": tail.value, "lookahead": True}
 

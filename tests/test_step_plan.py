@@ -14,9 +14,9 @@ B2(t-1), or by the S prologue for t = 0).
     - a swapped-in row additionally needs the ROWT pushes of its own column tile and of the tiles
       that hold block column t (this dependency once dead-locked when those pushes lived in a
       later phase);
-    - SCALE(t+1) of a column tile needs UPD(t) of the next pivot row on that tile: phase A (an
-      earlier launch), phase B1 (launched earlier, possibly still running beside B2, never waiting
-      for it) or the UPDP items at the head of B2 (lower claim index);
+    - SCALE(t+1) of a column tile needs UPD(t) of the next pivot row on that tile: phase A or B1
+      (earlier launches that never wait for B2) or the UPDP items at the head of B2 (lower claim
+      index);
 * the pivot-row buffer of parity (t+1)&1 that SCALE(t+1) overwrites is no longer read by step t-1
   (its readers are the phases of step t-1, all launched before K1(t+1), whose cross-rank min-loc
   every rank's B2(t) waits for): checked here as "SCALE(t+1) lives in B2(t), never earlier".
