@@ -191,7 +191,7 @@ def test_lookahead_schedule_is_bitwise_equal_to_serial(fid, n, m):
     # the tiles updated while K1 runs (0 and 1 are the degenerate splits)
     for env in ({"JB_SCHED": "1"}, {"JB_SCHED": "2"}, {"JB_SCHED": "2", "JB_B1_FRAC": "0.0"},
                 {"JB_SCHED": "1", "JB_B1_FRAC": "1.0"}, {"JB_SCHED": "2", "JB_B1_FRAC": "1.0"},
-                {"JB_SCHED": "2", "JB_K1_GATED": "1"}, {"JB_SCHED": "1", "JB_B2_OVERLAP": "1"}, {"JB_B2_OVERLAP": "1"}):
+                {"JB_SCHED": "2", "JB_K1_GATED": "1"}):
         Xl, pl, rl = _invert_w(n, m, fid, env)
         assert pl == ps, env
         assert torch.equal(Xl, Xs), (env, float((Xl - Xs).abs().max()))
