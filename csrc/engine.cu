@@ -91,8 +91,11 @@ struct JbEngine {
   int sched = 0;           // JB_SCHED: 1 = phase A in line (between B2(t-1) and B1(t)), else A beside B2(t-1)
   // B2(t) starts behind B1(t).  Letting it move in while B1 drains (JB_B2_OVERLAP=1: no event wait,
   // only the per-tile flags) measured no gain (0.3099 s against 0.3084-0.3123 s at 8 GPUs) and gave
-  // WRONG inverses at 8 GPUs, n = 32768 (residual 1e11; 2 GPUs were fine), cause not found: the
-  // switch is kept for debugging only.
+  // WRONG inverses at 8 GPUs, n = 32768.  Cause (found with tools/schedule_model.py): phase A(t+1)
+  // then starts while B1(t) may still run, and although the TMA producer thread waits for the flag
+  // of B1's early tile, the MMA warps read the C tile of that item from W as soon as it is handed
+  // to them - before B1's update of it.  Behind a finished B1 the pair cannot occur.  The switch is
+  // kept for debugging only; it needs that extra wait in the MMA warps before it may be used.
   bool b2_overlap = false;
   // tcgen05 split-precision update (precision = 1)
   bool tc05 = false;

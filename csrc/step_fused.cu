@@ -219,7 +219,10 @@ k_step_fused(const StepParams P, const __grid_constant__ StepMaps M) {
         if (!kScale || it.type != IT_SCALE) {
           if (kRowt && P.phase == JB_PHASE_A && (it.ct < P.prev_pct0 || it.ct > P.prev_pct1)) {
             // phase A runs beside the bulk of the previous step: this tile is one of B1(t-1)'s
-            // early tiles, flagged when every row carries update t-1
+            // early tiles, flagged when every row carries update t-1.  NOTE: this wait orders the
+            // TMA operand loads only; the MMA warps read the C tile of the item right after the
+            // hand-off.  That is fine because the engine launches phase A behind a FINISHED B1(t-1)
+            // (the flag is then already set); with JB_B2_OVERLAP the MMA warps would have to wait too.
             int j = it.ct - P.prev_pct1 - 1;
             if (j < 0) j += P.CT;
             if (j < 8) wait_flag_ge(P.early + 8 + j, P.prev_tag, abort_flag, spin_to);

@@ -16,7 +16,7 @@ from schedule_model import ScheduleModel  # noqa: E402
 
 @pytest.mark.parametrize("Nr,p", [(6, 1), (8, 2), (9, 3), (12, 4), (16, 8), (5, 8)])
 @pytest.mark.parametrize("kw", [dict(), dict(sched=1), dict(k1_gated=True), dict(frac=0.03), dict(frac=0.85),
-                                dict(sched=1, b2_overlap=True)])
+                                dict(sched=1, b2_overlap=True), dict(b2_overlap=True, mma_waits_early=True)])
 def test_no_unordered_conflicting_accesses(Nr, p, kw):
     mdl = ScheduleModel(Nr, p, **kw)
     assert mdl.hazards() == []
@@ -34,7 +34,7 @@ def test_model_finds_the_uncounted_row_install():
     must also count the install of block row t: phase A of the next step updates that row and K1
     copies it into the L panel.  (Behind a finished B1 - the default - the question does not arise.)"""
     assert ScheduleModel(8, 3, count_rowt_in_early=False).hazards() == []
-    hz = ScheduleModel(8, 3, count_rowt_in_early=False, b2_overlap=True).hazards()
+    hz = ScheduleModel(8, 3, count_rowt_in_early=False, b2_overlap=True, mma_waits_early=True).hazards()
     assert hz and all("ROWT" in h for h in hz)
 
 
@@ -58,3 +58,15 @@ def test_model_finds_the_unguarded_swap_push():
     assert ScheduleModel(12, 4, pivots=piv).hazards() == []
     hz = ScheduleModel(12, 4, pivots=piv, swap_handshake=False).hazards()
     assert hz and all("swapbuf" in h and "push" in h for h in hz)
+
+
+def test_model_explains_the_withdrawn_overlap_switch():
+    """JB_B2_OVERLAP=1 gave wrong inverses at 8 GPUs (profiles/README.md).  Why: in phase A the flag of
+    B1's early tile is awaited by the TMA producer thread only, while the MMA warps read the C tile
+    from W as soon as the item is handed to them - unordered with B1's update of that tile once B1
+    may still be running.  Behind a finished B1 (the default) and in the in-line schedule there is no
+    such pair; with the MMA warps waiting too the overlap would be clean."""
+    hz = ScheduleModel(16, 8, b2_overlap=True).hazards()
+    assert hz and all("C-read" in h and " A(" in h and " B1(" in h for h in hz)
+    assert ScheduleModel(16, 8, b2_overlap=True, mma_waits_early=True).hazards() == []
+    assert ScheduleModel(16, 8).hazards() == []

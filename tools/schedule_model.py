@@ -93,9 +93,10 @@ class ScheduleModel:
 
     def __init__(self, Nr: int, p: int, sched: int = 2, b2_overlap: bool = False, k1_gated: bool = False,
                  frac: float = 0.3, count_rowt_in_early: bool = True, stepdone_handshake: bool = True,
-                 pivots=None, swap_handshake: bool = True):
+                 pivots=None, swap_handshake: bool = True, mma_waits_early: bool = False):
         self.Nr, self.p, self.m = Nr, p, 128
         self.swap_handshake = swap_handshake
+        self.mma_waits_early = mma_waits_early      # False = the shipped kernel (see _row_item)
         self.pivots = list(pivots) if pivots is not None else list(range(Nr))
         assert len(self.pivots) == Nr and all(t <= g < Nr for t, g in enumerate(self.pivots))
         self.sched, self.b2_overlap, self.k1_gated, self.frac = sched, b2_overlap, k1_gated, frac
@@ -184,6 +185,13 @@ class ScheduleModel:
             return e, True
         e = g.node(lab + " end", s)
         self.waits.append((s, ("rowflag", t, ct)))
+        # The flag waits above are made by the TMA producer thread and order the operand loads.  The
+        # MMA warps read the C tile straight from W as soon as the item has been handed to them, i.e.
+        # possibly BEFORE those waits are over (csrc/step_fused.cu: the ring slot is published before
+        # the producer waits).  Only the swapped-in row's MMA warps wait themselves (swap flag).
+        c_start = s if (ty == UPD_SW or self.mma_waits_early) else g.node(lab + " C-read", ks)
+        if c_start is not s:
+            g.edge(c_start, e)
         self._access(("stepinfo", r, t), s, e, False, lab)
         for sb in range(self.nsub):
             self._access(("rowbuf", r, t & 1, ct, sb), s, e, False, lab)
@@ -194,7 +202,7 @@ class ScheduleModel:
                 self._access(("swapbuf", r, t & 1, c, sub), s, e, False, lab)
         else:
             self._access(("Lbuf", r, t % 3), s, e, False, lab)
-            self._access(("W", r, slot, sub, ct), s, e, False, lab)
+            self._access(("W", r, slot, sub, ct), c_start, e, False, lab + " C-read")
         self._access(("W", r, slot, sub, ct), s, e, True, lab)
         if prow:
             self._publish(("prow", r, t, ct, sub), e)
@@ -371,7 +379,7 @@ class ScheduleModel:
             writes = [x for x in lst if x[2]]
             for w in writes:
                 for o in lst:
-                    if o is w or o[0] == w[0] or (o[2] and id(o) < id(w)):   # same item / pair seen from the other side
+                    if o is w or o[1] == w[1] or (o[2] and id(o) < id(w)):   # same item / pair seen from the other side
                         continue
                     if self.before(w[1], o[0]) or self.before(o[1], w[0]):
                         continue
