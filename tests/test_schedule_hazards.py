@@ -70,3 +70,16 @@ def test_model_explains_the_withdrawn_overlap_switch():
     assert hz and all("C-read" in h and " A(" in h and " B1(" in h for h in hz)
     assert ScheduleModel(16, 8, b2_overlap=True, mma_waits_early=True).hazards() == []
     assert ScheduleModel(16, 8).hazards() == []
+
+
+@pytest.mark.parametrize("Nr,p,m", [(12, 2, 60), (12, 3, 64), (8, 2, 256), (9, 4, 256), (16, 8, 32), (10, 3, 96)])
+def test_other_block_sizes_straddling_the_column_tiles(Nr, p, m):
+    """m != 128: block columns straddle the 128-wide column tiles (m = 60 is BASELINE config 1, m = 256
+    config 3, m = 32 config 5), priority ranges and early tiles change shape from step to step."""
+    import random
+
+    rnd = random.Random(Nr * 100 + m)
+    piv = [rnd.choice([t, rnd.randrange(t, Nr)]) for t in range(Nr)]
+    assert ScheduleModel(Nr, p, m=m).hazards() == []
+    assert ScheduleModel(Nr, p, m=m, pivots=piv).hazards() == []
+    assert ScheduleModel(Nr, p, m=m, pivots=piv, sched=1).hazards() == []

@@ -87,23 +87,26 @@ def _enumerate(m, p, rank, rloc, ldw, t, piv_g, phase, pct0, pct1, nb1, nearly, 
 
 
 class ScheduleModel:
-    """Nr block rows of size m = 128 over p ranks.  pivots[t] = global block row chosen at step t
+    """Nr block rows of size m over p ranks (m = 128 unless given; other sizes make block columns
+    straddle the 128-wide column tiles).  pivots[t] = global block row chosen at step t
     (>= t; default: the diagonal).  A pivot off the diagonal adds the block-row swap: ROWT pushes the
     old row t into the pivot owner's swap buffer, the swapped-in row is updated from there."""
 
     def __init__(self, Nr: int, p: int, sched: int = 2, b2_overlap: bool = False, k1_gated: bool = False,
                  frac: float = 0.3, count_rowt_in_early: bool = True, stepdone_handshake: bool = True,
-                 pivots=None, swap_handshake: bool = True, mma_waits_early: bool = False):
-        self.Nr, self.p, self.m = Nr, p, 128
+                 pivots=None, swap_handshake: bool = True, mma_waits_early: bool = False, m: int = 128):
+        self.Nr, self.p, self.m = Nr, p, m
         self.swap_handshake = swap_handshake
         self.mma_waits_early = mma_waits_early      # False = the shipped kernel (see _row_item)
         self.pivots = list(pivots) if pivots is not None else list(range(Nr))
         assert len(self.pivots) == Nr and all(t <= g < Nr for t, g in enumerate(self.pivots))
         self.sched, self.b2_overlap, self.k1_gated, self.frac = sched, b2_overlap, k1_gated, frac
         self.count_rowt_in_early, self.stepdone_handshake = count_rowt_in_early, stepdone_handshake
-        self.CT = Nr                       # m == BN: one column tile per block column
-        self.nsub = 2
-        self.ldw = Nr * self.m
+        from mpi_jordan_crazy_acceleration_b200.parallel.layout import padded_ld
+
+        self.ldw = padded_ld(Nr * m, m)
+        self.CT = (self.ldw + BN - 1) // BN    # block columns may straddle column tiles (m != 128)
+        self.nsub = (m + 63) // 64
         self.g = Graph()
         self.flag: dict = {}               # flag key -> list of producer end nodes (published when all ended)
         self.waits: list = []              # (waiting node, flag key)
@@ -129,6 +132,9 @@ class ScheduleModel:
             nb1 = nnp
         return pct0, pct1, nnp, nearly, nb1
 
+    def tiles_of_block_col(self, t):
+        return range((t * self.m) // BN, ((t + 1) * self.m - 1) // BN + 1)
+
     def np_pos(self, t, ct):
         pct0, pct1 = self.pri(t)
         return ct - pct1 - 1 if ct > pct1 else ct + self.CT - pct1 - 1
@@ -148,7 +154,8 @@ class ScheduleModel:
         lab = f"r{r} K1({t})"
         for slot in range(self.rloc(r)):
             for sub in range(self.nsub):
-                self._access(("W", r, slot, sub, t), s, e, False, lab)   # block column t of every local row
+                for ct in self.tiles_of_block_col(t):                   # block column t of every local row
+                    self._access(("W", r, slot, sub, ct), s, e, False, lab)
         self._access(("Lbuf", r, t % 3), s, e, True, lab)
         self._access(("invbuf", r, t & 1), s, e, True, lab)
         self._access(("stepinfo", r, t), s, e, True, lab)
@@ -165,7 +172,7 @@ class ScheduleModel:
         s = g.node(lab + " start", ks)
         if wait_prev_early is not None:
             self.waits.append((s, wait_prev_early))
-        tile_t = (t * m) // BN                      # column tile holding block column t (m == BN)
+        tiles_t = set(self.tiles_of_block_col(t))   # column tiles holding block column t
         if ty == ROWT:
             cur = s
             if do_swap:                             # push the old row t to the pivot owner (main.cpp:1100-1131)
@@ -197,7 +204,7 @@ class ScheduleModel:
             self._access(("rowbuf", r, t & 1, ct, sb), s, e, False, lab)
         if ty == UPD_SW:
             assert do_swap and r == piv_rank and slot == piv_slot
-            for c in {tile_t, ct}:
+            for c in tiles_t | {ct}:
                 self.waits.append((s, ("swapflag", t, c, sub)))
                 self._access(("swapbuf", r, t & 1, c, sub), s, e, False, lab)
         else:
