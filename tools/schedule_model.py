@@ -224,6 +224,10 @@ class ScheduleModel:
                            nxt % p if nxt >= 0 else -1, nxt // p if nxt >= 0 else 0)
         name = {PH_A: "A", PH_S: "S", PH_B1: "B1", PH_B2: "B2"}[phase]
         ks = stream.op(f"r{r} {name}({t}) start", *preds)
+        # every CTA reads stepinfo[t] (B2: also stepinfo[t+1]) when it starts, before any flag wait
+        self._access(("stepinfo", r, t), ks, ks, False, f"r{r} {name}({t}) prologue")
+        if nxt >= 0:
+            self._access(("stepinfo", r, t + 1), ks, ks, False, f"r{r} {name}({t}) prologue")
         ends = []
         c0 = nb1 if phase == PH_B2 else 0
         early_items = defaultdict(list)
