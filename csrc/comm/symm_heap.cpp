@@ -252,23 +252,31 @@ int jb_symm_heap_import(JbSymmHeap* h, const int* fds) {
   Drv* d = drv();
   if (!d || !h) return JB_ERR_ARG;
   cudaSetDevice(h->device);
+  int rc = JB_OK;
   for (int r = 0; r < h->size; ++r) {
     if (r == h->rank) continue;
     if (fds[r] < 0) {
-      jb_set_error("symm_heap: no descriptor for rank %d", r);
-      return JB_ERR_ARG;
+      if (rc == JB_OK) {
+        jb_set_error("symm_heap: no descriptor for rank %d", r);
+        rc = JB_ERR_ARG;
+      }
+      continue;
+    }
+    if (rc != JB_OK) {  // an earlier peer failed: still close what we were handed
+      close(fds[r]);
+      continue;
     }
     CUresult cr = d->MemImportFromShareableHandle(&h->peer_handles[r], (void*)(uintptr_t)fds[r],
                                                   CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
     close(fds[r]);
     if (cr != CUDA_SUCCESS) {
       jb_set_error("symm_heap: import of rank %d's allocation failed: %s", r, errstr(d, cr));
-      return JB_ERR_CUDA;
+      rc = JB_ERR_CUDA;
+      continue;
     }
-    int rc = map_rw(d, h, &h->va[r], h->peer_handles[r]);
-    if (rc != JB_OK) return rc;
+    rc = map_rw(d, h, &h->va[r], h->peer_handles[r]);
   }
-  return JB_OK;
+  return rc;
 }
 
 int jb_symm_heap_multicast_supported(const JbSymmHeap* h) { return h && h->mc_supported ? 1 : 0; }

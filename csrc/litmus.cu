@@ -115,23 +115,31 @@ extern "C" int jb_store_bandwidth(void* dst, size_t bytes, int mode, int iters, 
     return JB_ERR_ARG;
   }
   double* sink = nullptr;
-  JB_CHECK(cudaMalloc((void**)&sink, 8));
-  cudaEvent_t e0, e1;
-  JB_CHECK(cudaEventCreate(&e0));
-  JB_CHECK(cudaEventCreate(&e1));
-  const size_t pairs = bytes / 16;
-  k_store_bw<<<148 * 8, 256>>>((double*)dst, pairs, mode, sink);
-  JB_CHECK(cudaDeviceSynchronize());
-  JB_CHECK(cudaEventRecord(e0));
-  for (int i = 0; i < iters; ++i) k_store_bw<<<148 * 8, 256>>>((double*)dst, pairs, mode, sink);
-  JB_CHECK(cudaEventRecord(e1));
-  JB_CHECK(cudaEventSynchronize(e1));
-  JB_CHECK(cudaGetLastError());
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
   float ms = 0;
-  JB_CHECK(cudaEventElapsedTime(&ms, e0, e1));
-  *ms_out = ms / iters;
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
+  cudaError_t ce = cudaMalloc((void**)&sink, 8);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&e0);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&e1);
+  const size_t pairs = bytes / 16;
+  if (ce == cudaSuccess) {
+    k_store_bw<<<148 * 8, 256>>>((double*)dst, pairs, mode, sink);
+    ce = cudaDeviceSynchronize();
+  }
+  if (ce == cudaSuccess) ce = cudaEventRecord(e0);
+  if (ce == cudaSuccess) {
+    for (int i = 0; i < iters; ++i) k_store_bw<<<148 * 8, 256>>>((double*)dst, pairs, mode, sink);
+    ce = cudaEventRecord(e1);
+  }
+  if (ce == cudaSuccess) ce = cudaEventSynchronize(e1);
+  if (ce == cudaSuccess) ce = cudaGetLastError();
+  if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
   cudaFree(sink);
+  if (ce != cudaSuccess) {
+    jb_set_error("jb_store_bandwidth: %s", cudaGetErrorString(ce));
+    return JB_ERR_CUDA;
+  }
+  *ms_out = ms / iters;
   return JB_OK;
 }
